@@ -1,0 +1,316 @@
+/*
+ * foremast_cuda.h — C ABI of libforemast_cuda.so
+ *
+ * The batched canary-vs-baseline anomaly-scoring path of Foremast's brain
+ * (moving-average mean +- k*sigma bounds, Mann-Whitney / Wilcoxon /
+ * Kruskal-Wallis rank tests, verdict and roll-up), as sm_100a CUDA behind a
+ * plain C interface.  Paths below are relative to the reference tree.
+ *
+ * The reference has no in-process plugin API for this path: foremast-service
+ * writes an Elasticsearch document (foremast-service/pkg/models/models.go:83-101,
+ * pkg/search/elasticsearchstore.go:22-62) and the brain (a separate Python
+ * program, foremast-brain/README.md:1-38, not in the tree) polls it, scores it
+ * and writes status/reason/anomalyInfo back (models.go:136-138,
+ * pkg/converter/converter.go:11-30).  Each entry point here therefore cites the
+ * reference text that defines the behaviour it implements; the binding a
+ * maintainer adds on the reference side (cgo / ctypes) is in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns int32_t: FM_OK (0) or a negative FM_E_* code;
+ *     fm_last_error(ctx) gives a ctx-owned message valid until the next call.
+ *   - all structs are POD; structs that may grow start with `struct_size`.
+ *   - rows are series-major fp32, time-ascending, NaN-free (gaps are compacted
+ *     by the host), `pitch` is in ELEMENTS, must be a multiple of 4 and the
+ *     matrix base pointer must be 16-byte aligned (rows are moved with 16-byte
+ *     bulk copies).  Per-row valid lengths are optional (NULL = every row has
+ *     n_* valid points).
+ *   - one ctx <-> one GPU <-> one stream; calls on one ctx must be serialised
+ *     by the caller, different ctxs are independent.
+ *   - no CPU fallback: without a usable CUDA device every compute entry point
+ *     fails with FM_E_NODEVICE.
+ */
+#ifndef FOREMAST_CUDA_H_
+#define FOREMAST_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FM_VERSION_MAJOR 0
+#define FM_VERSION_MINOR 1
+
+/* ---- error codes ------------------------------------------------------- */
+#define FM_OK              0
+#define FM_E_INVALID      -1  /* bad argument / layout contract violated      */
+#define FM_E_CUDA         -2  /* CUDA runtime error (see fm_last_error)        */
+#define FM_E_NOMEM        -3  /* host or device allocation failed              */
+#define FM_E_UNSUPPORTED  -4  /* shape outside the limits stated below         */
+#define FM_E_NODEVICE     -5  /* no CUDA device / driver                       */
+
+/* ---- verdicts (design.md:25,43; converter.go:17-22) -------------------- */
+#define FM_HEALTHY   0u  /* -> "completed_health"   */
+#define FM_UNHEALTHY 1u  /* -> "completed_unhealth" */
+#define FM_UNKNOWN   2u  /* -> "completed_unknown"  */
+
+/* ---- per-series status bits -------------------------------------------- */
+#define FM_ST_HIST_INSUFFICIENT 0x01u /* fewer than min_hist_points in the model window */
+#define FM_ST_NO_CURRENT        0x02u /* no current points ("unknown", design.md:25)   */
+#define FM_ST_DIFFER            0x04u /* pairwise says distributions differ: k_low used */
+#define FM_ST_PAIRWISE_SKIPPED  0x08u /* pairwise requested but no eligible test        */
+#define FM_ST_MW_RUN            0x10u /* Mann-Whitney evaluated                         */
+#define FM_ST_WX_RUN            0x20u /* Wilcoxon evaluated                             */
+#define FM_ST_KW_RUN            0x40u /* Kruskal-Wallis evaluated                       */
+#define FM_ST_DEGENERATE        0x80u /* an evaluated test had zero variance: its p = 1 */
+
+/* ---- strategies (metricsquery.go:17-19; BASELINE.json spellings) ------- */
+#define FM_STRAT_CANARY      0u /* cur + base (+ hist): pairwise tests + bounds       */
+#define FM_STRAT_HISTORICAL  1u /* cur + hist only: rollingUpdate/continuous/hpa      */
+
+/* ---- moving-average model (foremast-brain.yaml:24-25) ------------------ */
+#define FM_MA_ALL     0u  /* moving_average_all: one mean/sigma over the whole window */
+#define FM_MA_WINDOW  1u  /* trailing window of ma_window points                      */
+#define FM_MODEL_EWMA        2u /* exponential smoothing (design.md:60-66)            */
+#define FM_MODEL_DOUBLE_EXP  3u /* double exponential smoothing (Holt linear)         */
+
+/* ---- pairwise mode (foremast-brain/README.md:34) ----------------------- */
+#define FM_PW_NONE       0u
+#define FM_PW_MANN_WHITE 1u
+#define FM_PW_WILCOXON   2u
+#define FM_PW_KRUSKAL    3u
+#define FM_PW_ALL        4u
+#define FM_PW_ANY        5u
+
+#define FM_PAIR_HEAD 0u
+#define FM_PAIR_TAIL 1u
+
+#define FM_REC_FULL    0u  /* fm_series_rec, 96 B   */
+#define FM_REC_COMPACT 1u  /* fm_compact_rec, 16 B  */
+
+/* limits of this build */
+#define FM_MAX_TYPES      64u
+#define FM_MAX_CUR        4096u   /* n_cur (canary / group length)                 */
+#define FM_MAX_RANK_N     16384u  /* n_cur + n_base, and sum of group lengths      */
+#define FM_MAX_GROUPS     16u     /* Kruskal-Wallis groups per service             */
+
+typedef struct fm_ctx fm_ctx;
+
+/* Per metric-type thresholds: threshold{i}/bound{i}/min_lower_bound{i} of
+ * deploy/foremast/3_brain/foremast-brain.yaml:26-73.  bound_mask: 1 = upper,
+ * 2 = lower, 3 = both (README.md:24). k_low is the "lower threshold" used when
+ * baseline and current differ (design.md:35). */
+typedef struct {
+  double   k;
+  double   k_low;
+  double   min_lower_bound;
+  uint32_t bound_mask;
+  uint32_t reserved;
+} fm_type_params;
+
+/* Global knobs: ML_ALGORITHM, MIN_HISTORICAL_DATA_POINT_TO_MEASURE,
+ * ML_PAIRWISE_ALGORITHM, ML_PAIRWISE_THRESHOLD, MIN_*_DATA_POINTS
+ * (README.md:22-38; foremast-brain.yaml:74-79). */
+typedef struct {
+  uint32_t struct_size;
+  uint32_t ddof;               /* 0 or 1                                   */
+  uint32_t ma_mode;            /* FM_MA_* / FM_MODEL_*                     */
+  uint32_t ma_window;          /* w for FM_MA_WINDOW                       */
+  uint32_t min_hist_points;    /* default 10                               */
+  uint32_t pairwise_mode;      /* FM_PW_*                                  */
+  uint32_t min_mw, min_wx, min_kw;   /* 20 / 20 / 5                        */
+  uint32_t cc_mw, cc_wx;       /* continuity correction on/off (1 / 0)     */
+  uint32_t pair_rule;          /* FM_PAIR_HEAD / FM_PAIR_TAIL              */
+  uint32_t min_anomaly_points; /* default 1 (fail fast, design.md:43)      */
+  uint32_t reserved;
+  double   alpha;              /* ML_PAIRWISE_THRESHOLD, default 0.05      */
+  double   smooth_alpha;       /* level factor for FM_MODEL_EWMA/DOUBLE_EXP */
+  double   smooth_beta;        /* trend factor for FM_MODEL_DOUBLE_EXP      */
+} fm_global_params;
+
+/* Full per-series result, 96 B.  U1/W are exact half-integers; p-values and
+ * H are fp64.  Tests that were not evaluated report stat = 0, p = 1. */
+typedef struct {
+  double   mean, sigma, upper, lower;   /* model + bounds (gauges _upper/_lower, metrics.js:14-20) */
+  double   u1, p_u;                     /* Mann-Whitney U of the current sample, two-sided p        */
+  double   w,  p_w;                     /* Wilcoxon min(W+,W-), two-sided p                         */
+  double   h,  p_h;                     /* Kruskal-Wallis H (tie corrected), chi2 p                 */
+  uint32_t n_anom;                      /* anomalous current points                                 */
+  uint16_t first_idx;                   /* first anomalous index, 0xFFFF if none                    */
+  uint8_t  verdict;                     /* FM_HEALTHY / FM_UNHEALTHY / FM_UNKNOWN                   */
+  uint8_t  status;                      /* FM_ST_* bits                                             */
+  uint64_t anom_mask;                   /* bit i = current point i anomalous (first 64 points)      */
+} fm_series_rec;
+
+typedef struct {
+  uint64_t anom_mask;
+  uint32_t n_anom;
+  uint8_t  verdict;
+  uint8_t  status;
+  uint16_t first_idx;
+} fm_compact_rec;
+
+/* Exact integer rank statistics, for parity checks (optional output). */
+typedef struct {
+  int64_t r2_cur;      /* 2 * (rank sum of the current sample in cur U base)      */
+  int64_t t_mw;        /* sum (t^3 - t) over tie runs of cur U base               */
+  int64_t w2_plus;     /* 2 * W+                                                   */
+  int64_t w2_minus;    /* 2 * W-                                                   */
+  int64_t t_wx;        /* sum (t^3 - t) over tie runs of the non-zero |d|          */
+  uint32_t n_wx;       /* non-zero differences used by Wilcoxon                    */
+  uint32_t reserved;
+} fm_rank_aux;
+
+/* Roll-up of child verdicts (README.md:26; rule A.9 in DESIGN.md). */
+typedef struct {
+  uint32_t n_children;
+  uint32_t n_unhealthy;
+  uint32_t n_unknown;
+  uint8_t  severity;    /* FM_HEALTHY / FM_UNHEALTHY / FM_UNKNOWN */
+  uint8_t  reserved[3];
+} fm_rollup_rec;
+
+/* A batch of independent series.  The same struct describes host rows
+ * (fm_score_batch) and device-resident rows (fm_score_batch_device). */
+typedef struct {
+  uint32_t struct_size;
+  uint32_t strategy;        /* FM_STRAT_*                                          */
+  uint64_t n_series;
+  const float*    cur;   const uint32_t* cur_len;   uint32_t n_cur;   uint32_t cur_pitch;
+  const float*    base;  const uint32_t* base_len;  uint32_t n_base;  uint32_t base_pitch;
+  const float*    hist;  const uint32_t* hist_len;  uint32_t n_hist;  uint32_t hist_pitch;
+                            /* hist == NULL with a baseline: the model window is the baseline row */
+  const uint8_t*  metric_type;  /* index into the fm_set_params table, NULL = type 0 everywhere  */
+  const uint32_t* api_id;       /* non-decreasing, < n_apis; NULL = no roll-up                    */
+  const uint32_t* api_service;  /* [n_apis] non-decreasing, < n_services                          */
+  uint32_t n_apis;
+  uint32_t n_services;
+  uint32_t record_kind;     /* FM_REC_FULL / FM_REC_COMPACT                        */
+  uint32_t reserved;
+} fm_batch;
+
+/* Rollover strategy: Kruskal-Wallis over the pod groups of each service
+ * (BASELINE.json configs[3]; README.md:34 KRUSKAL).  Rows of `cur` are groups;
+ * service v owns rows group_offsets[v] .. group_offsets[v+1]-1 (3..FM_MAX_GROUPS
+ * typical); every group is also bound-checked against the service's pooled
+ * historical row. */
+typedef struct {
+  uint32_t struct_size;
+  uint32_t reserved;
+  uint64_t n_services;
+  uint64_t n_groups;
+  const uint32_t* group_offsets;   /* [n_services + 1] */
+  const float*    cur;   const uint32_t* cur_len;   uint32_t n_cur;   uint32_t cur_pitch;   /* [n_groups] rows   */
+  const float*    hist;  const uint32_t* hist_len;  uint32_t n_hist;  uint32_t hist_pitch;  /* [n_services] rows */
+  const uint8_t*  metric_type;     /* [n_services] */
+} fm_group_batch;
+
+typedef struct {
+  float    kernel_ms;      /* device time of the scoring launches (CUDA events on the ctx stream) */
+  uint32_t launches;       /* kernels launched by this call                                        */
+  float    h2d_ms, d2h_ms; /* fm_score_batch only: copy engine time, 0 otherwise                  */
+  uint64_t h2d_bytes, d2h_bytes;
+} fm_timing;
+
+/* Synthetic workload descriptor (generator: include/fm_synth.h). */
+typedef struct {
+  uint32_t struct_size;
+  uint32_t config;         /* 1..5 = BASELINE.json configs, value families per metric type */
+  uint64_t seed;
+  uint64_t first_series;   /* global id of row 0 (sharding by series id)                    */
+  uint64_t n_series;
+  uint32_t n_cur, n_base, n_hist;
+  uint32_t cur_pitch, base_pitch, hist_pitch;
+} fm_synth_desc;
+
+/* ------------------------------------------------------------------------ */
+
+/* (major << 16) | minor. */
+int32_t fm_version(void);
+
+/* Number of usable CUDA devices (0 and FM_OK when none). */
+int32_t fm_device_count(int32_t* out);
+
+/* Bind a GPU, create the stream and the grow-only device arenas.  Replaces the
+ * brain process start-up (one brain pod == one scoring worker,
+ * docs/guides/design.md:37-41). */
+int32_t fm_ctx_create(int32_t device, fm_ctx** out);
+int32_t fm_ctx_destroy(fm_ctx* ctx);
+
+/* Fill `g` / `table[0..5]` with the deployed defaults of
+ * deploy/foremast/3_brain/foremast-brain.yaml:24-79 (type 0 = default,
+ * 1 error5xx, 2 error4xx, 3 latency, 4 cpu, 5 memory).  *n_types in: capacity,
+ * out: 6. */
+int32_t fm_default_params(fm_global_params* g, fm_type_params* table, uint32_t* n_types);
+
+/* Install parameters on a ctx (the env-var block of foremast-brain.yaml:21-81). */
+int32_t fm_set_params(fm_ctx* ctx, const fm_global_params* g,
+                      const fm_type_params* table, uint32_t n_types);
+
+/* Pinned host memory for row matrices and result arrays. */
+int32_t fm_alloc_pinned(size_t bytes, void** out);
+int32_t fm_free_pinned(void* p);
+
+/* Device memory helpers for callers that keep rows resident (bench, tests). */
+int32_t fm_device_alloc(fm_ctx* ctx, size_t bytes, void** out);
+int32_t fm_device_free(fm_ctx* ctx, void* p);
+int32_t fm_memcpy_h2d(fm_ctx* ctx, void* dst, const void* src, size_t bytes);
+int32_t fm_memcpy_d2h(fm_ctx* ctx, void* dst, const void* src, size_t bytes);
+
+/* Score a batch whose rows are in HOST memory; results land in host arrays.
+ * This is the call the brain's job loop makes per poll: historical model ->
+ * pairwise test -> lowered threshold -> anomaly points -> verdict
+ * (docs/guides/design.md:35,43; foremast-brain/README.md:5-10).  Synchronous.
+ * out_records: n_series records of batch->record_kind.  out_aux, out_api,
+ * out_svc may be NULL.  Host->device copies are chunked and overlapped with
+ * scoring; `timing` may be NULL. */
+int32_t fm_score_batch(fm_ctx* ctx, const fm_batch* batch, void* out_records,
+                       fm_rank_aux* out_aux, fm_rollup_rec* out_api,
+                       fm_rollup_rec* out_svc, fm_timing* timing);
+
+/* Same, with every pointer in `batch` and every output a DEVICE pointer.
+ * Asynchronous on the ctx stream unless `timing` is non-NULL (then it
+ * synchronises to read the events). */
+int32_t fm_score_batch_device(fm_ctx* ctx, const fm_batch* batch, void* d_out_records,
+                              fm_rank_aux* d_out_aux, fm_rollup_rec* d_out_api,
+                              fm_rollup_rec* d_out_svc, fm_timing* timing);
+
+/* Rollover strategy (Kruskal-Wallis over pod groups).  out_group_records:
+ * n_groups fm_series_rec (model/bounds/anomalies per group, H and p_h of its
+ * service); out_svc: n_services roll-ups over the groups, may be NULL. */
+int32_t fm_score_groups(fm_ctx* ctx, const fm_group_batch* batch,
+                        fm_series_rec* out_group_records, fm_rollup_rec* out_svc,
+                        fm_timing* timing);
+int32_t fm_score_groups_device(fm_ctx* ctx, const fm_group_batch* batch,
+                               fm_series_rec* d_out_group_records, fm_rollup_rec* d_out_svc,
+                               fm_timing* timing);
+
+/* Parity aid: 2 * midrank of every point of cur U base (cur first), one series,
+ * host pointers.  r2_out has n_cur + n_base entries. */
+int32_t fm_rank_dump(fm_ctx* ctx, const float* cur, uint32_t n_cur,
+                     const float* base, uint32_t n_base, uint32_t* r2_out);
+
+/* Trailing-window moving average series (gauges _upper/_lower over time,
+ * foremast-browser/src/config/metrics.js:14-20): for one host row x[0..n),
+ * writes mean_t and sigma_t for t >= w-1 (NaN before). */
+int32_t fm_ma_window_series(fm_ctx* ctx, const float* x, uint32_t n, uint32_t w,
+                            uint32_t ddof, double* mean_out, double* sigma_out);
+
+/* Synthetic rows, bit-identical on host and device (include/fm_synth.h).
+ * The *_device variant writes device matrices, the *_host variant host ones. */
+int32_t fm_synth_fill_device(fm_ctx* ctx, const fm_synth_desc* d, float* d_cur,
+                             float* d_base, float* d_hist, uint8_t* d_metric_type);
+int32_t fm_synth_fill_host(const fm_synth_desc* d, float* cur, float* base,
+                           float* hist, uint8_t* metric_type, uint32_t n_threads);
+
+/* Block until all work queued on the ctx stream has finished. */
+int32_t fm_ctx_sync(fm_ctx* ctx);
+
+/* Message for the last failing call on this ctx (NULL ctx: last create error). */
+const char* fm_last_error(fm_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FOREMAST_CUDA_H_ */
