@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py — series scored / second on BASELINE.json's headline workload.
+
+A step is one pass of the scoring path over one batch of synthetic series:
+config 3 (1M series x 60-point canary vs 1440-point baseline; moving-average
+bounds + Mann-Whitney + Wilcoxon (+ 2-group Kruskal), verdict) per GPU, sharded
+by series id with no collective (weak scaling: every rank owns 1M series of an
+N x 1M job).  `value` is measured with the rows resident in HBM (CUDA events on
+the library's stream, max over ranks); `e2e` goes through fm_score_batch with
+pinned HOST rows, host<->device copies inside the timed region.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+WORKLOADS = {
+    # name: (config id, n_cur, n_base, n_hist, strategy, pairwise mode name, default series/GPU)
+    "c3": dict(config=3, n_cur=60, n_base=1440, n_hist=0, canary=True, mode="ANY", series=1_000_000,
+               desc="config 3: 1M series x (60-pt canary vs 1440-pt baseline), MA + Mann-Whitney + Wilcoxon"),
+    "c2": dict(config=2, n_cur=60, n_base=1440, n_hist=10080, canary=True, mode="MANN_WHITE", series=10_000,
+               desc="config 2: 10k series, 60-pt canary vs 1440 baseline, MA on 10080-pt history + Mann-Whitney"),
+    "c5": dict(config=5, n_cur=60, n_base=0, n_hist=1440, canary=False, mode="NONE", series=1_000_000,
+               desc="config 5 slice: MA-only bounds on 1440-pt history + roll-up"),
+}
+
+
+def algorithmic_bytes(w, rec_bytes):
+    """4*(n_cur + n_base + n_hist') + R, each sample counted once."""
+    return 4 * (w["n_cur"] + w["n_base"] + w["n_hist"]) + rec_bytes
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def params_for(w):
+    from foremast_1_b200 import _abi as A
+    g, table = A.default_params()
+    g.pairwise_mode = getattr(A, "FM_PW_" + w["mode"])
+    return g, table
+
+
+def cpu_baseline(w, budget_s=12.0, threads=None):
+    """The oracle (a port: the reference tree holds no implementation) on the host cores,
+    on a bounded sample of the same synthetic workload."""
+    import oracle_lib as O
+    from foremast_1_b200 import _abi as A
+    from foremast_1_b200.engine import synth_desc
+    g, table = params_for(w)
+    threads = threads or os.cpu_count() or 1
+    strat = A.FM_STRAT_CANARY if w["canary"] else A.FM_STRAT_HISTORICAL
+    hist_is_base = w["canary"] and w["n_hist"] == 0
+    d = synth_desc(w["config"], 32 * threads, w["n_cur"], w["n_base"], w["n_hist"])
+    secs, _ = O.bench_synth(g, table, d, strat, hist_is_base, threads)
+    rate = d.n_series / max(secs, 1e-9)
+    n = int(max(32 * threads, min(rate * budget_s, 4_000_000)))
+    d = synth_desc(w["config"], n, w["n_cur"], w["n_base"], w["n_hist"])
+    secs, chk = O.bench_synth(g, table, d, strat, hist_is_base, threads)
+    return {"value": n / secs, "unit": "series/s", "cores": threads, "kind": "port",
+            "sample": f"{n} series of the same synthetic workload (ids 0..{n - 1}), scoring time only, "
+                      f"{secs:.2f} s on {threads} threads"}, n, secs
+
+
+def run_reference(args, w, rank):
+    """--impl reference: the reference's CPU path = the oracle port, all host threads."""
+    if rank != 0:
+        return
+    import oracle_lib as O
+    from foremast_1_b200 import _abi as A
+    from foremast_1_b200.engine import synth_desc
+    g, table = params_for(w)
+    threads = os.cpu_count() or 1
+    strat = A.FM_STRAT_CANARY if w["canary"] else A.FM_STRAT_HISTORICAL
+    hist_is_base = w["canary"] and w["n_hist"] == 0
+    d = synth_desc(w["config"], 32 * threads, w["n_cur"], w["n_base"], w["n_hist"])
+    secs, _ = O.bench_synth(g, table, d, strat, hist_is_base, threads)
+    rate = d.n_series / max(secs, 1e-9)
+    total_steps = args.steps + args.warmup
+    per_step_s = max(1.0, min(8.0, 90.0 / max(total_steps, 1)))
+    n = int(max(32 * threads, rate * per_step_s))
+    d = synth_desc(w["config"], n, w["n_cur"], w["n_base"], w["n_hist"])
+    for _ in range(args.warmup):
+        O.bench_synth(g, table, d, strat, hist_is_base, threads)
+    tot = 0.0
+    for _ in range(args.steps):
+        s, _ = O.bench_synth(g, table, d, strat, hist_is_base, threads)
+        tot += s
+    v = n * args.steps / tot
+    line = {"impl": "reference", "metric": "series scored/sec", "value": v, "unit": "series/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": w["desc"], "series_per_step": n, "n_cur": w["n_cur"],
+                       "n_base": w["n_base"], "n_hist": w["n_hist"], "pairwise": w["mode"]},
+            "cpu_baseline": {"value": v, "unit": "series/s", "cores": threads, "kind": "port",
+                             "sample": f"{n} series per step, oracle port (reference holds no brain code)"},
+            "e2e": {"value": v, "unit": "series/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--series", type=int, default=0, help="series per GPU (default: the workload's)")
+    ap.add_argument("--e2e-series", type=int, default=0, help="series per fm_score_batch call (default: --series)")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    w = dict(WORKLOADS[args.workload])
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, w, rank)
+        return
+    if args.warmup < 3:
+        args.warmup = 3
+
+    import ctypes as C
+    import numpy as np
+    import torch
+    from foremast_1_b200 import _abi as A
+    from foremast_1_b200.engine import Context, Pinned, synth_desc
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def rank_max(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    S = args.series or w["series"]
+    ctx = Context(local)
+    g, table = params_for(w)
+    ctx.set_params(g, table)
+    strat = A.FM_STRAT_CANARY if w["canary"] else A.FM_STRAT_HISTORICAL
+    d = synth_desc(w["config"], S, w["n_cur"], w["n_base"], w["n_hist"], first_series=rank * S)
+    d_cur = ctx.dev_alloc(S * d.cur_pitch * 4)
+    d_base = ctx.dev_alloc(S * d.base_pitch * 4) if w["n_base"] else None
+    d_hist = ctx.dev_alloc(S * d.hist_pitch * 4) if w["n_hist"] else None
+    d_mt = ctx.dev_alloc(S)
+    d_out = ctx.dev_alloc(S * A.SERIES_REC.itemsize)
+    ctx.synth_device(d, d_cur, d_base, d_hist, d_mt)
+    ctx.sync()
+
+    b = A.Batch()
+    b.struct_size = C.sizeof(A.Batch)
+    b.strategy = strat
+    b.n_series = S
+    b.cur, b.n_cur, b.cur_pitch = d_cur, w["n_cur"], d.cur_pitch
+    if d_base:
+        b.base, b.n_base, b.base_pitch = d_base, w["n_base"], d.base_pitch
+    if d_hist:
+        b.hist, b.n_hist, b.hist_pitch = d_hist, w["n_hist"], d.hist_pitch
+    b.metric_type = d_mt
+    b.record_kind = A.FM_REC_FULL
+
+    t = A.Timing()
+    for _ in range(args.warmup):
+        ctx.score_device(b, d_out, timing=t)
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    wall0 = time.perf_counter()
+    dev_ms, main_ms, launches = 0.0, 0.0, 0
+    for _ in range(args.steps):
+        ctx.score_device(b, d_out, timing=t)
+        dev_ms += t.kernel_ms
+        main_ms += t.main_kernel_ms
+        launches += t.launches
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - wall0)
+    clocks = sampler.stop()
+    dev_ms_max = rank_max(dev_ms)
+    main_ms_max = rank_max(main_ms)
+    value = world * S * args.steps / (dev_ms_max / 1e3)
+
+    # sanity: verdict histogram of the last step (also proves the kernel wrote results)
+    rec = np.zeros(min(S, 65536), A.SERIES_REC)
+    ctx.d2h(rec, d_out)
+    hist_v = np.bincount(rec["verdict"], minlength=3).tolist()
+
+    # ---- end to end: pinned host rows through fm_score_batch ----------------
+    e2e = None
+    if not args.no_e2e:
+        Se = args.e2e_series or S
+        try:
+            import psutil
+            need = Se * 4 * (d.cur_pitch + d.base_pitch + d.hist_pitch) * max(1, world)
+            if need * 3 > psutil.virtual_memory().available:
+                Se = max(4096, int(Se * psutil.virtual_memory().available / (need * 3)))
+        except Exception:
+            pass
+        de = synth_desc(w["config"], Se, w["n_cur"], w["n_base"], w["n_hist"], first_series=rank * S)
+        p_cur = Pinned((Se, de.cur_pitch), np.float32)
+        p_base = Pinned((Se, de.base_pitch), np.float32) if w["n_base"] else None
+        p_hist = Pinned((Se, de.hist_pitch), np.float32) if w["n_hist"] else None
+        p_mt = Pinned((Se,), np.uint8)
+        p_out = Pinned((Se,), A.SERIES_REC)
+        from foremast_1_b200 import _ffi
+        rc = _ffi.lib().fm_synth_fill_host(C.byref(de), p_cur.ptr, p_base.ptr if p_base else None,
+                                           p_hist.ptr if p_hist else None, p_mt.ptr, 0)
+        assert rc == 0
+        hb = A.Batch()
+        hb.struct_size = C.sizeof(A.Batch)
+        hb.strategy = strat
+        hb.n_series = Se
+        hb.cur, hb.n_cur, hb.cur_pitch = p_cur.ptr, w["n_cur"], de.cur_pitch
+        if p_base:
+            hb.base, hb.n_base, hb.base_pitch = p_base.ptr, w["n_base"], de.base_pitch
+        if p_hist:
+            hb.hist, hb.n_hist, hb.hist_pitch = p_hist.ptr, w["n_hist"], de.hist_pitch
+        hb.metric_type = p_mt.ptr
+        hb.record_kind = A.FM_REC_FULL
+        te = A.Timing()
+        ctx.score_host(hb, p_out.ptr, timing=te)   # warm-up (arena growth, first touch)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            ctx.score_host(hb, p_out.ptr, timing=te)
+            launches_e2e = te.launches
+        barrier()
+        e_s = rank_max(time.perf_counter() - t0)
+        # the first records of the e2e pass must equal the device-resident pass
+        same = bool((p_out.array[: rec.size] == rec[: min(rec.size, Se)]).all()) if Se >= rec.size else None
+        e2e = {"value": world * Se * args.e2e_steps / e_s, "unit": "series/s",
+               "h2d_bytes_per_step": int(te.h2d_bytes), "d2h_bytes_per_step": int(te.d2h_bytes),
+               "series_per_step_per_gpu": Se, "steps": args.e2e_steps, "ms_per_step": 1e3 * e_s / args.e2e_steps,
+               "launches_per_step": int(launches_e2e), "matches_device_pass": same}
+        for pbuf in (p_cur, p_base, p_hist, p_mt, p_out):
+            if pbuf:
+                pbuf.free()
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        rec_bytes = A.SERIES_REC.itemsize
+        bps = algorithmic_bytes(w, rec_bytes)
+        achieved = S * bps / (main_ms_max / args.steps / 1e3) / 1e9
+        line = {
+            "metric": "series scored/sec", "value": value, "unit": "series/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms_max / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": w["desc"], "series_per_gpu": S, "n_cur": w["n_cur"], "n_base": w["n_base"],
+                       "n_hist": w["n_hist"], "pairwise": w["mode"], "sharding": "by series id, no collective",
+                       "l2": "inputs (%.1f GB/GPU) larger than L2" % (S * (bps - rec_bytes) / 1e9),
+                       "timing": "CUDA events on the library stream, per step, max over ranks"},
+            "wall_ms_per_step": wall_ms / args.steps,
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "bytes_per_series": bps, "kernel": "k_score_series",
+                         "kernel_ms": main_ms_max / args.steps},
+            "verdict_histogram_first_64k": hist_v,
+        }
+        if e2e is not None:
+            line["e2e"] = e2e
+        if world == 1 and not args.no_cpu:
+            cb, _, _ = cpu_baseline(w)
+            line["cpu_baseline"] = cb
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -70,14 +70,16 @@ class GroupBatch(C.Structure):
 
 class Timing(C.Structure):
     _fields_ = [("kernel_ms", C.c_float), ("launches", C.c_uint32), ("h2d_ms", C.c_float),
-                ("d2h_ms", C.c_float), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+                ("d2h_ms", C.c_float), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("main_kernel_ms", C.c_float), ("reserved", C.c_uint32)]
 
 
 class SynthDesc(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("config", C.c_uint32), ("seed", C.c_uint64),
                 ("first_series", C.c_uint64), ("n_series", C.c_uint64),
                 ("n_cur", C.c_uint32), ("n_base", C.c_uint32), ("n_hist", C.c_uint32),
-                ("cur_pitch", C.c_uint32), ("base_pitch", C.c_uint32), ("hist_pitch", C.c_uint32)]
+                ("cur_pitch", C.c_uint32), ("base_pitch", C.c_uint32), ("hist_pitch", C.c_uint32),
+                ("row_ids", C.c_void_p)]
 
 
 # numpy views of the result records (same layout as the C structs)

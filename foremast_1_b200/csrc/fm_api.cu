@@ -1,0 +1,704 @@
+// fm_api.cu — host side of the C ABI (include/foremast_cuda.h): contexts, device
+// arenas, launch planning, and the chunked host->device pipeline.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/fm_synth.h"
+#include "fm_internal.h"
+
+namespace {
+
+struct Arena {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    const size_t want = (bytes + 255) & ~size_t(255);
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+thread_local std::string g_create_error;
+
+}  // namespace
+
+struct fm_ctx {
+  int device = 0;
+  int num_sms = 148;
+  size_t smem_optin = 0;
+  cudaStream_t stream = nullptr;   // compute
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_m = nullptr;
+  FmParamsDev params;
+  FmParamsDev* d_params = nullptr;
+  // staging for fm_score_batch: two chunk slots
+  Arena in[2], out[2], roll, misc;
+  cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
+  std::vector<cudaEvent_t> kev;    // per-chunk kernel timing events
+  int score_smem_set = 0, groups_smem_set = 0;
+  std::string err;
+};
+
+namespace {
+
+int32_t fail(fm_ctx* c, int32_t code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+  if (c) c->err = buf; else g_create_error = buf;
+  return code;
+}
+
+#define FM_CK(ctx, call)                                                              \
+  do {                                                                                \
+    cudaError_t e__ = (call);                                                         \
+    if (e__ != cudaSuccess)                                                           \
+      return fail(ctx, e__ == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_CUDA,     \
+                  "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__,  \
+                  __LINE__);                                                          \
+  } while (0)
+
+uint32_t pow2_ceil(uint32_t n, uint32_t lo) { uint32_t p = lo; while (p < n) p <<= 1; return p; }
+uint32_t round4(uint32_t n) { return (n + 3u) & ~3u; }
+
+bool mode_has(uint32_t mode, uint32_t t) { return mode == t || mode == FM_PW_ALL || mode == FM_PW_ANY; }
+
+struct Plan { FmKArgs a; int wpc; int grid; };
+
+// Shared-memory layout and launch shape for k_score_series.
+int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
+  FmKArgs& a = pl->a;
+  memset(&a, 0, sizeof(a));
+  const bool canary = b->strategy == FM_STRAT_CANARY && b->base != nullptr;
+  if (b->n_cur > FM_MAX_CUR) return fail(c, FM_E_UNSUPPORTED, "n_cur %u > %u", b->n_cur, FM_MAX_CUR);
+  if (canary && (uint64_t)b->n_cur + b->n_base > FM_MAX_RANK_N)
+    return fail(c, FM_E_UNSUPPORTED, "n_cur + n_base %u > %u", b->n_cur + b->n_base, FM_MAX_RANK_N);
+  a.cur_cap = std::max(4u, round4(b->n_cur));
+  a.cs_cap = pow2_ceil(b->n_cur, 64u);
+  a.base_cap = canary ? pow2_ceil(b->n_base, 64u) : 0u;
+  const bool wx = canary && mode_has(c->params.g.pairwise_mode, FM_PW_WILCOXON) &&
+                  c->params.g.pairwise_mode != FM_PW_NONE;
+  a.wx_n = wx ? ((std::min(b->n_cur, b->n_base) + 1u) & ~1u) : 0u;
+  a.wx_cap = wx ? pow2_ceil(a.wx_n, 64u) : 0u;
+  auto bytes = [&](uint32_t stages) {
+    size_t x = 16 + (size_t)stages * (a.cur_cap + a.base_cap) * 4 + (size_t)a.cs_cap * 4 +
+               (size_t)a.wx_n * 8 + (size_t)a.wx_cap * 8;
+    return (x + 127) & ~size_t(127);
+  };
+  const size_t limit = c->smem_optin ? c->smem_optin : 232448;
+  const size_t sm_total = 233472 - 1024;  // 228 KB per SM, 1 KB reserved per CTA
+  a.n_stages = 2;
+  if (bytes(2) > limit) a.n_stages = 1;
+  // large rows: rather keep a few warps per SM than double buffer each of them
+  if (a.n_stages == 2 && sm_total / bytes(2) < 4 && sm_total / bytes(1) >= 2 * (sm_total / bytes(2)))
+    a.n_stages = 1;
+  if (bytes(1) > limit) return fail(c, FM_E_UNSUPPORTED, "series too long for shared memory (%zu B per warp)", bytes(1));
+  a.warp_bytes = (uint32_t)bytes(a.n_stages);
+  // warps per CTA and CTAs per SM: fill the SM's shared memory, at most 16 warps per CTA
+  int wpc = (int)std::min<size_t>(16, limit / a.warp_bytes);
+  if (wpc < 1) wpc = 1;
+  int ctas = (int)std::min<size_t>(4, sm_total / ((size_t)wpc * a.warp_bytes + 1024));
+  if (ctas < 1) ctas = 1;
+  while (ctas * wpc > 64) --ctas;
+  pl->wpc = wpc;
+  const uint64_t need = (b->n_series + wpc - 1) / wpc;
+  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * ctas, need));
+  const int smem = wpc * (int)a.warp_bytes;
+  if (smem > c->score_smem_set) {
+    FM_CK(c, fm_score_smem_attr((int)limit));
+    c->score_smem_set = (int)limit;
+  }
+  a.cur = b->cur; a.cur_len = b->cur_len; a.n_cur = b->n_cur; a.cur_pitch = b->cur_pitch;
+  a.base = canary ? b->base : nullptr; a.base_len = b->base_len; a.n_base = canary ? b->n_base : 0; a.base_pitch = b->base_pitch;
+  a.hist = b->hist; a.hist_len = b->hist_len; a.n_hist = b->n_hist; a.hist_pitch = b->hist_pitch;
+  a.metric_type = b->metric_type; a.api_id = b->api_id;
+  a.n_series = b->n_series;
+  a.P = c->d_params;
+  a.record_kind = b->record_kind;
+  a.strategy = b->strategy;
+  return FM_OK;
+}
+
+int32_t validate_batch(fm_ctx* c, const fm_batch* b, const void* out) {
+  if (!c) return FM_E_INVALID;
+  if (!b || !out) return fail(c, FM_E_INVALID, "null batch or output");
+  if (b->struct_size != sizeof(fm_batch)) return fail(c, FM_E_INVALID, "fm_batch.struct_size %u != %zu", b->struct_size, sizeof(fm_batch));
+  if (b->strategy > FM_STRAT_HISTORICAL) return fail(c, FM_E_INVALID, "unknown strategy %u", b->strategy);
+  if (b->record_kind > FM_REC_COMPACT) return fail(c, FM_E_INVALID, "unknown record kind %u", b->record_kind);
+  if (b->n_series && !b->cur && b->n_cur) return fail(c, FM_E_INVALID, "cur is NULL");
+  auto bad = [](const float* p, uint32_t n, uint32_t pitch) {
+    return p && ((reinterpret_cast<uintptr_t>(p) & 15u) || (pitch & 3u) || pitch < ((n + 3u) & ~3u));
+  };
+  if (bad(b->cur, b->n_cur, b->cur_pitch) || bad(b->base, b->n_base, b->base_pitch) ||
+      bad(b->hist, b->n_hist, b->hist_pitch))
+    return fail(c, FM_E_INVALID, "rows must be 16-byte aligned with pitch a multiple of 4 and >= roundup4(n)");
+  if (b->api_id && b->n_apis == 0) return fail(c, FM_E_INVALID, "api_id given but n_apis == 0");
+  return FM_OK;
+}
+
+size_t rec_size(uint32_t kind) { return kind == FM_REC_COMPACT ? sizeof(fm_compact_rec) : sizeof(fm_series_rec); }
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+extern "C" {
+
+int32_t fm_version(void) { return (FM_VERSION_MAJOR << 16) | FM_VERSION_MINOR; }
+
+uint32_t fm_sizeof(uint32_t which) {
+  switch (which) {
+    case 0: return sizeof(fm_global_params);
+    case 1: return sizeof(fm_type_params);
+    case 2: return sizeof(fm_batch);
+    case 3: return sizeof(fm_group_batch);
+    case 4: return sizeof(fm_series_rec);
+    case 5: return sizeof(fm_compact_rec);
+    case 6: return sizeof(fm_rank_aux);
+    case 7: return sizeof(fm_rollup_rec);
+    case 8: return sizeof(fm_timing);
+    case 9: return sizeof(fm_synth_desc);
+    default: return 0;
+  }
+}
+
+int32_t fm_device_count(int32_t* out) {
+  if (!out) return FM_E_INVALID;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }
+  *out = n;
+  return FM_OK;
+}
+
+int32_t fm_default_params(fm_global_params* g, fm_type_params* table, uint32_t* n_types) {
+  if (!g || !table || !n_types || *n_types < 6) return FM_E_INVALID;
+  memset(g, 0, sizeof(*g));
+  g->struct_size = sizeof(*g);
+  g->ddof = 0; g->ma_mode = FM_MA_ALL; g->ma_window = 0; g->min_hist_points = 10;
+  g->pairwise_mode = FM_PW_ANY; g->min_mw = 20; g->min_wx = 20; g->min_kw = 5;
+  g->cc_mw = 1; g->cc_wx = 0; g->pair_rule = FM_PAIR_HEAD; g->min_anomaly_points = 1;
+  g->alpha = 0.05; g->smooth_alpha = 0.3; g->smooth_beta = 0.1;
+  // foremast-brain.yaml:26-73: default, error5xx, error4xx, latency, cpu, memory
+  const double k[6] = {2.0, 2.0, 3.0, 10.0, 5.0, 5.0};
+  const uint32_t bound[6] = {1, 1, 1, 3, 1, 1};
+  for (int i = 0; i < 6; ++i) {
+    table[i].k = k[i]; table[i].k_low = 0.5 * k[i]; table[i].min_lower_bound = 0.0;
+    table[i].bound_mask = bound[i]; table[i].reserved = 0;
+  }
+  *n_types = 6;
+  return FM_OK;
+}
+
+int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
+  if (!out) return FM_E_INVALID;
+  *out = nullptr;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(nullptr, FM_E_NODEVICE, "no CUDA device available (libforemast_cuda has no CPU fallback)");
+  }
+  if (device < 0 || device >= n) return fail(nullptr, FM_E_INVALID, "device %d out of range [0,%d)", device, n);
+  fm_ctx* c = new (std::nothrow) fm_ctx();
+  if (!c) return FM_E_NOMEM;
+  c->device = device;
+#define FM_CKC(call)                                                                           \
+  do {                                                                                         \
+    cudaError_t e__ = (call);                                                                  \
+    if (e__ != cudaSuccess) {                                                                  \
+      fail(nullptr, FM_E_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__));               \
+      delete c;                                                                                \
+      return FM_E_CUDA;                                                                        \
+    }                                                                                          \
+  } while (0)
+  FM_CKC(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  FM_CKC(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    { fail(nullptr, FM_E_UNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); delete c; return FM_E_UNSUPPORTED; }
+  c->num_sms = prop.multiProcessorCount;
+  c->smem_optin = prop.sharedMemPerBlockOptin;
+  FM_CKC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  FM_CKC(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
+  FM_CKC(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
+  FM_CKC(cudaEventCreate(&c->ev_a));
+  FM_CKC(cudaEventCreate(&c->ev_b));
+  FM_CKC(cudaEventCreate(&c->ev_m));
+  for (int i = 0; i < 2; ++i) {
+    FM_CKC(cudaEventCreateWithFlags(&c->in_ready[i], cudaEventDisableTiming));
+    FM_CKC(cudaEventCreateWithFlags(&c->in_free[i], cudaEventDisableTiming));
+    FM_CKC(cudaEventCreateWithFlags(&c->out_ready[i], cudaEventDisableTiming));
+    FM_CKC(cudaEventCreateWithFlags(&c->out_free[i], cudaEventDisableTiming));
+  }
+  FM_CKC(cudaMalloc(&c->d_params, sizeof(FmParamsDev)));
+#undef FM_CKC
+  memset(&c->params, 0, sizeof(c->params));
+  uint32_t nt = FM_MAX_TYPES;
+  fm_default_params(&c->params.g, c->params.types, &nt);
+  c->params.n_types = nt;
+  cudaError_t e = cudaMemcpy(c->d_params, &c->params, sizeof(FmParamsDev), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { fail(nullptr, FM_E_CUDA, "params upload: %s", cudaGetErrorString(e)); fm_ctx_destroy(c); return FM_E_CUDA; }
+  *out = c;
+  return FM_OK;
+}
+
+int32_t fm_ctx_destroy(fm_ctx* c) {
+  if (!c) return FM_OK;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  for (int i = 0; i < 2; ++i) {
+    c->in[i].release(); c->out[i].release();
+    if (c->in_ready[i]) cudaEventDestroy(c->in_ready[i]);
+    if (c->in_free[i]) cudaEventDestroy(c->in_free[i]);
+    if (c->out_ready[i]) cudaEventDestroy(c->out_ready[i]);
+    if (c->out_free[i]) cudaEventDestroy(c->out_free[i]);
+  }
+  for (cudaEvent_t e : c->kev) cudaEventDestroy(e);
+  c->roll.release(); c->misc.release();
+  if (c->d_params) cudaFree(c->d_params);
+  if (c->ev_a) cudaEventDestroy(c->ev_a);
+  if (c->ev_b) cudaEventDestroy(c->ev_b);
+  if (c->ev_m) cudaEventDestroy(c->ev_m);
+  if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
+  if (c->s_d2h) cudaStreamDestroy(c->s_d2h);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return FM_OK;
+}
+
+int32_t fm_set_params(fm_ctx* c, const fm_global_params* g, const fm_type_params* table, uint32_t n_types) {
+  if (!c) return FM_E_INVALID;
+  if (!g || !table || n_types == 0 || n_types > FM_MAX_TYPES) return fail(c, FM_E_INVALID, "bad params (n_types %u)", n_types);
+  if (g->struct_size != sizeof(fm_global_params)) return fail(c, FM_E_INVALID, "fm_global_params.struct_size %u != %zu", g->struct_size, sizeof(fm_global_params));
+  if (g->ddof > 1 || g->ma_mode > FM_MODEL_DOUBLE_EXP || g->pairwise_mode > FM_PW_ANY || g->pair_rule > FM_PAIR_TAIL)
+    return fail(c, FM_E_INVALID, "parameter out of range");
+  FM_CK(c, cudaSetDevice(c->device));
+  c->params.g = *g;
+  c->params.n_types = n_types;
+  memcpy(c->params.types, table, n_types * sizeof(fm_type_params));
+  // a barrier on the ctx: queued launches read the old table
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  FM_CK(c, cudaMemcpy(c->d_params, &c->params, sizeof(FmParamsDev), cudaMemcpyHostToDevice));
+  return FM_OK;
+}
+
+int32_t fm_alloc_pinned(size_t bytes, void** out) {
+  if (!out) return FM_E_INVALID;
+  *out = nullptr;
+  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable);
+  if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_NODEVICE; }
+  return FM_OK;
+}
+int32_t fm_free_pinned(void* p) { if (p) cudaFreeHost(p); return FM_OK; }
+
+int32_t fm_device_alloc(fm_ctx* c, size_t bytes, void** out) {
+  if (!c || !out) return FM_E_INVALID;
+  FM_CK(c, cudaSetDevice(c->device));
+  FM_CK(c, cudaMalloc(out, bytes ? bytes : 1));
+  return FM_OK;
+}
+int32_t fm_device_free(fm_ctx* c, void* p) {
+  if (!c) return FM_E_INVALID;
+  FM_CK(c, cudaSetDevice(c->device));
+  if (p) FM_CK(c, cudaFree(p));
+  return FM_OK;
+}
+int32_t fm_memcpy_h2d(fm_ctx* c, void* dst, const void* src, size_t bytes) {
+  if (!c) return FM_E_INVALID;
+  FM_CK(c, cudaSetDevice(c->device));
+  FM_CK(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  return FM_OK;
+}
+int32_t fm_memcpy_d2h(fm_ctx* c, void* dst, const void* src, size_t bytes) {
+  if (!c) return FM_E_INVALID;
+  FM_CK(c, cudaSetDevice(c->device));
+  FM_CK(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  return FM_OK;
+}
+int32_t fm_ctx_sync(fm_ctx* c) {
+  if (!c) return FM_E_INVALID;
+  FM_CK(c, cudaSetDevice(c->device));
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  return FM_OK;
+}
+
+const char* fm_last_error(fm_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+// ---------------------------------------------------------------------------
+int32_t fm_score_batch_device(fm_ctx* c, const fm_batch* b, void* d_out, fm_rank_aux* d_aux,
+                              fm_rollup_rec* d_api, fm_rollup_rec* d_svc, fm_timing* timing) {
+  int32_t rc = validate_batch(c, b, d_out);
+  if (rc != FM_OK) return rc;
+  FM_CK(c, cudaSetDevice(c->device));
+  if (timing) memset(timing, 0, sizeof(*timing));
+  if (b->n_series == 0) return FM_OK;
+  Plan pl;
+  rc = plan_score(c, b, &pl);
+  if (rc != FM_OK) return rc;
+  pl.a.out = d_out; pl.a.aux = d_aux;
+  const bool roll = b->api_id && d_api;
+  pl.a.api = roll ? d_api : nullptr;
+  uint32_t launches = 0;
+  if (roll) {
+    FM_CK(c, cudaMemsetAsync(d_api, 0, (size_t)b->n_apis * sizeof(fm_rollup_rec), c->stream));
+    if (d_svc && b->api_service) FM_CK(c, cudaMemsetAsync(d_svc, 0, (size_t)b->n_services * sizeof(fm_rollup_rec), c->stream));
+  }
+  if (timing) FM_CK(c, cudaEventRecord(c->ev_a, c->stream));
+  launches += fm_launch_score(pl.a, pl.wpc, pl.grid, c->stream);
+  if (timing) FM_CK(c, cudaEventRecord(c->ev_m, c->stream));
+  if (roll)
+    launches += fm_launch_rollup_finalize(d_api, b->n_apis, b->api_service,
+                                          (d_svc && b->api_service) ? d_svc : nullptr, b->n_services, c->stream);
+  FM_CK(c, cudaGetLastError());
+  if (timing) {
+    FM_CK(c, cudaEventRecord(c->ev_b, c->stream));
+    FM_CK(c, cudaEventSynchronize(c->ev_b));
+    FM_CK(c, cudaEventElapsedTime(&timing->kernel_ms, c->ev_a, c->ev_b));
+    FM_CK(c, cudaEventElapsedTime(&timing->main_kernel_ms, c->ev_a, c->ev_m));
+    timing->launches = launches;
+  }
+  return FM_OK;
+}
+
+int32_t fm_score_batch(fm_ctx* c, const fm_batch* b, void* out, fm_rank_aux* out_aux,
+                       fm_rollup_rec* out_api, fm_rollup_rec* out_svc, fm_timing* timing) {
+  int32_t rc = validate_batch(c, b, out);
+  if (rc != FM_OK) return rc;
+  FM_CK(c, cudaSetDevice(c->device));
+  if (timing) memset(timing, 0, sizeof(*timing));
+  const uint64_t S = b->n_series;
+  if (S == 0) return FM_OK;
+  const bool canary = b->strategy == FM_STRAT_CANARY && b->base != nullptr;
+  const bool roll = b->api_id && out_api && b->n_apis;
+  const bool roll_svc = roll && out_svc && b->api_service && b->n_services;
+  const size_t rsz = rec_size(b->record_kind);
+
+  // chunking: ~64 MB of rows per chunk, two slots in flight
+  const size_t row_bytes = 4 * ((size_t)b->cur_pitch + (canary ? b->base_pitch : 0) + (b->hist ? b->hist_pitch : 0));
+  uint64_t chunk = row_bytes ? (size_t(64) << 20) / row_bytes : S;
+  chunk = std::max<uint64_t>(chunk, 2048);
+  chunk = std::min<uint64_t>(chunk, S);
+  const uint64_t n_chunks = (S + chunk - 1) / chunk;
+
+  // per-slot input layout (all offsets 256-byte aligned)
+  auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
+  size_t o = 0;
+  const size_t o_cur = o;  o += al(chunk * b->cur_pitch * 4);
+  const size_t o_base = o; o += canary ? al(chunk * b->base_pitch * 4) : 0;
+  const size_t o_hist = o; o += b->hist ? al(chunk * b->hist_pitch * 4) : 0;
+  const size_t o_clen = o; o += b->cur_len ? al(chunk * 4) : 0;
+  const size_t o_blen = o; o += (canary && b->base_len) ? al(chunk * 4) : 0;
+  const size_t o_hlen = o; o += (b->hist && b->hist_len) ? al(chunk * 4) : 0;
+  const size_t o_mt = o;   o += b->metric_type ? al(chunk) : 0;
+  const size_t o_api = o;  o += roll ? al(chunk * 4) : 0;
+  const size_t in_bytes = o;
+  const size_t o_rec = 0;
+  const size_t o_aux = al(chunk * rsz);
+  const size_t out_bytes = o_aux + (out_aux ? al(chunk * sizeof(fm_rank_aux)) : 0);
+  const int slots = n_chunks > 1 ? 2 : 1;
+  for (int i = 0; i < slots; ++i) { FM_CK(c, c->in[i].reserve(in_bytes)); FM_CK(c, c->out[i].reserve(out_bytes)); }
+  fm_rollup_rec *d_api = nullptr, *d_svc = nullptr;
+  uint32_t* d_api_service = nullptr;
+  if (roll) {
+    const size_t a0 = al((size_t)b->n_apis * sizeof(fm_rollup_rec));
+    const size_t a1 = roll_svc ? al((size_t)b->n_services * sizeof(fm_rollup_rec)) : 0;
+    const size_t a2 = roll_svc ? al((size_t)b->n_apis * 4) : 0;
+    FM_CK(c, c->roll.reserve(a0 + a1 + a2));
+    d_api = static_cast<fm_rollup_rec*>(c->roll.p);
+    FM_CK(c, cudaMemsetAsync(c->roll.p, 0, a0 + a1, c->stream));
+    if (roll_svc) {
+      d_svc = reinterpret_cast<fm_rollup_rec*>(static_cast<char*>(c->roll.p) + a0);
+      d_api_service = reinterpret_cast<uint32_t*>(static_cast<char*>(c->roll.p) + a0 + a1);
+      FM_CK(c, cudaMemcpyAsync(d_api_service, b->api_service, (size_t)b->n_apis * 4, cudaMemcpyHostToDevice, c->stream));
+    }
+  }
+  while (c->kev.size() < 2 * n_chunks) {
+    cudaEvent_t e; FM_CK(c, cudaEventCreate(&e)); c->kev.push_back(e);
+  }
+
+  uint32_t launches = 0;
+  uint64_t h2d = 0, d2h = 0;
+  for (uint64_t ci = 0; ci < n_chunks; ++ci) {
+    const int s = (int)(ci & 1);
+    const uint64_t s0 = ci * chunk, n = std::min(chunk, S - s0);
+    char* din = static_cast<char*>(c->in[s].p);
+    char* dout = static_cast<char*>(c->out[s].p);
+    // host -> device on the copy stream, once the slot's previous kernel is done
+    if (ci >= 2) FM_CK(c, cudaStreamWaitEvent(c->s_h2d, c->in_free[s], 0));
+    auto up = [&](size_t off, const void* src, size_t bytes) -> cudaError_t {
+      h2d += bytes;
+      return cudaMemcpyAsync(din + off, src, bytes, cudaMemcpyHostToDevice, c->s_h2d);
+    };
+    FM_CK(c, up(o_cur, b->cur + s0 * b->cur_pitch, n * b->cur_pitch * 4));
+    if (canary) FM_CK(c, up(o_base, b->base + s0 * b->base_pitch, n * b->base_pitch * 4));
+    if (b->hist) FM_CK(c, up(o_hist, b->hist + s0 * b->hist_pitch, n * b->hist_pitch * 4));
+    if (b->cur_len) FM_CK(c, up(o_clen, b->cur_len + s0, n * 4));
+    if (canary && b->base_len) FM_CK(c, up(o_blen, b->base_len + s0, n * 4));
+    if (b->hist && b->hist_len) FM_CK(c, up(o_hlen, b->hist_len + s0, n * 4));
+    if (b->metric_type) FM_CK(c, up(o_mt, b->metric_type + s0, n));
+    if (roll) FM_CK(c, up(o_api, b->api_id + s0, n * 4));
+    FM_CK(c, cudaEventRecord(c->in_ready[s], c->s_h2d));
+
+    // score on the compute stream
+    fm_batch db = *b;
+    db.n_series = n;
+    db.cur = reinterpret_cast<const float*>(din + o_cur);
+    db.base = canary ? reinterpret_cast<const float*>(din + o_base) : nullptr;
+    db.hist = b->hist ? reinterpret_cast<const float*>(din + o_hist) : nullptr;
+    db.cur_len = b->cur_len ? reinterpret_cast<const uint32_t*>(din + o_clen) : nullptr;
+    db.base_len = (canary && b->base_len) ? reinterpret_cast<const uint32_t*>(din + o_blen) : nullptr;
+    db.hist_len = (b->hist && b->hist_len) ? reinterpret_cast<const uint32_t*>(din + o_hlen) : nullptr;
+    db.metric_type = b->metric_type ? reinterpret_cast<const uint8_t*>(din + o_mt) : nullptr;
+    db.api_id = roll ? reinterpret_cast<const uint32_t*>(din + o_api) : nullptr;
+    Plan pl;
+    rc = plan_score(c, &db, &pl);
+    if (rc != FM_OK) return rc;
+    pl.a.out = dout + o_rec;
+    pl.a.aux = out_aux ? reinterpret_cast<fm_rank_aux*>(dout + o_aux) : nullptr;
+    pl.a.api = roll ? d_api : nullptr;
+    FM_CK(c, cudaStreamWaitEvent(c->stream, c->in_ready[s], 0));
+    if (ci >= 2) FM_CK(c, cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
+    FM_CK(c, cudaEventRecord(c->kev[2 * ci], c->stream));
+    launches += fm_launch_score(pl.a, pl.wpc, pl.grid, c->stream);
+    FM_CK(c, cudaGetLastError());
+    FM_CK(c, cudaEventRecord(c->kev[2 * ci + 1], c->stream));
+    FM_CK(c, cudaEventRecord(c->in_free[s], c->stream));
+    FM_CK(c, cudaEventRecord(c->out_ready[s], c->stream));
+
+    // device -> host on the read-back stream
+    FM_CK(c, cudaStreamWaitEvent(c->s_d2h, c->out_ready[s], 0));
+    FM_CK(c, cudaMemcpyAsync(static_cast<char*>(out) + s0 * rsz, dout + o_rec, n * rsz, cudaMemcpyDeviceToHost, c->s_d2h));
+    d2h += n * rsz;
+    if (out_aux) {
+      FM_CK(c, cudaMemcpyAsync(out_aux + s0, dout + o_aux, n * sizeof(fm_rank_aux), cudaMemcpyDeviceToHost, c->s_d2h));
+      d2h += n * sizeof(fm_rank_aux);
+    }
+    FM_CK(c, cudaEventRecord(c->out_free[s], c->s_d2h));
+  }
+  if (roll) {
+    launches += fm_launch_rollup_finalize(d_api, b->n_apis, d_api_service, d_svc, b->n_services, c->stream);
+    FM_CK(c, cudaGetLastError());
+    FM_CK(c, cudaMemcpyAsync(out_api, d_api, (size_t)b->n_apis * sizeof(fm_rollup_rec), cudaMemcpyDeviceToHost, c->stream));
+    d2h += (size_t)b->n_apis * sizeof(fm_rollup_rec);
+    if (roll_svc) {
+      FM_CK(c, cudaMemcpyAsync(out_svc, d_svc, (size_t)b->n_services * sizeof(fm_rollup_rec), cudaMemcpyDeviceToHost, c->stream));
+      d2h += (size_t)b->n_services * sizeof(fm_rollup_rec);
+    }
+  }
+  FM_CK(c, cudaStreamSynchronize(c->s_h2d));
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  FM_CK(c, cudaStreamSynchronize(c->s_d2h));
+  if (timing) {
+    float tot = 0.f;
+    for (uint64_t ci = 0; ci < n_chunks; ++ci) {
+      float ms = 0.f;
+      FM_CK(c, cudaEventElapsedTime(&ms, c->kev[2 * ci], c->kev[2 * ci + 1]));
+      tot += ms;
+    }
+    timing->kernel_ms = tot; timing->main_kernel_ms = tot; timing->launches = launches;
+    timing->h2d_bytes = h2d; timing->d2h_bytes = d2h;
+  }
+  return FM_OK;
+}
+
+// ---------------------------------------------------------------------------
+static int32_t plan_groups(fm_ctx* c, const fm_group_batch* b, FmGArgs* a, int* wpc, int* grid) {
+  memset(a, 0, sizeof(*a));
+  if (!b || b->struct_size != sizeof(fm_group_batch)) return fail(c, FM_E_INVALID, "bad fm_group_batch");
+  if (!b->group_offsets || (!b->cur && b->n_groups)) return fail(c, FM_E_INVALID, "null group_offsets / cur");
+  if ((uint64_t)b->n_cur * FM_MAX_GROUPS > FM_MAX_RANK_N) return fail(c, FM_E_UNSUPPORTED, "n_cur %u too long for %u groups", b->n_cur, FM_MAX_GROUPS);
+  if ((b->cur_pitch & 3u) || (b->hist && (b->hist_pitch & 3u)) || (reinterpret_cast<uintptr_t>(b->hist) & 15u))
+    return fail(c, FM_E_INVALID, "rows must be 16-byte aligned with pitch a multiple of 4");
+  a->raw_cap = std::max(64u, b->n_cur * FM_MAX_GROUPS);
+  a->pool_cap = pow2_ceil(a->raw_cap, 64u);
+  a->warp_bytes = (uint32_t)((((size_t)a->raw_cap + a->pool_cap) * 4 + 127) & ~size_t(127));
+  const size_t limit = c->smem_optin ? c->smem_optin : 232448;
+  if (a->warp_bytes > limit) return fail(c, FM_E_UNSUPPORTED, "groups too long for shared memory");
+  *wpc = (int)std::max<size_t>(1, std::min<size_t>(16, limit / a->warp_bytes));
+  if (c->groups_smem_set == 0) { FM_CK(c, fm_groups_smem_attr((int)limit)); c->groups_smem_set = 1; }
+  const uint64_t need = (b->n_services + *wpc - 1) / *wpc;
+  int ctas = (int)std::max<size_t>(1, std::min<size_t>(4, (233472 - 1024) / ((size_t)*wpc * a->warp_bytes + 1024)));
+  *grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * ctas, need));
+  a->group_offsets = b->group_offsets;
+  a->cur = b->cur; a->cur_len = b->cur_len; a->n_cur = b->n_cur; a->cur_pitch = b->cur_pitch;
+  a->hist = b->hist; a->hist_len = b->hist_len; a->n_hist = b->n_hist; a->hist_pitch = b->hist_pitch;
+  a->metric_type = b->metric_type;
+  a->n_services = b->n_services;
+  a->P = c->d_params;
+  return FM_OK;
+}
+
+int32_t fm_score_groups_device(fm_ctx* c, const fm_group_batch* b, fm_series_rec* d_out,
+                               fm_rollup_rec* d_svc, fm_timing* timing) {
+  if (!c) return FM_E_INVALID;
+  if (!d_out) return fail(c, FM_E_INVALID, "null output");
+  FM_CK(c, cudaSetDevice(c->device));
+  if (timing) memset(timing, 0, sizeof(*timing));
+  FmGArgs a; int wpc = 1, grid = 1;
+  int32_t rc = plan_groups(c, b, &a, &wpc, &grid);
+  if (rc != FM_OK) return rc;
+  if (b->n_services == 0) return FM_OK;
+  a.out = d_out; a.svc = d_svc;
+  uint32_t launches = 0;
+  if (d_svc) FM_CK(c, cudaMemsetAsync(d_svc, 0, b->n_services * sizeof(fm_rollup_rec), c->stream));
+  if (timing) FM_CK(c, cudaEventRecord(c->ev_a, c->stream));
+  launches += fm_launch_groups(a, wpc, grid, c->stream);
+  if (timing) FM_CK(c, cudaEventRecord(c->ev_m, c->stream));
+  launches += fm_launch_rollup_finalize_one(d_svc, b->n_services, c->stream);
+  FM_CK(c, cudaGetLastError());
+  if (timing) {
+    FM_CK(c, cudaEventRecord(c->ev_b, c->stream));
+    FM_CK(c, cudaEventSynchronize(c->ev_b));
+    FM_CK(c, cudaEventElapsedTime(&timing->kernel_ms, c->ev_a, c->ev_b));
+    FM_CK(c, cudaEventElapsedTime(&timing->main_kernel_ms, c->ev_a, c->ev_m));
+    timing->launches = launches;
+  }
+  return FM_OK;
+}
+
+int32_t fm_score_groups(fm_ctx* c, const fm_group_batch* b, fm_series_rec* out, fm_rollup_rec* out_svc,
+                        fm_timing* timing) {
+  if (!c) return FM_E_INVALID;
+  if (!b || !out) return fail(c, FM_E_INVALID, "null batch or output");
+  if (b->struct_size != sizeof(fm_group_batch)) return fail(c, FM_E_INVALID, "bad fm_group_batch.struct_size");
+  FM_CK(c, cudaSetDevice(c->device));
+  auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
+  const uint64_t V = b->n_services, G = b->n_groups;
+  size_t o = 0;
+  const size_t o_off = o;  o += al((V + 1) * 4);
+  const size_t o_cur = o;  o += al(G * b->cur_pitch * 4);
+  const size_t o_clen = o; o += b->cur_len ? al(G * 4) : 0;
+  const size_t o_hist = o; o += b->hist ? al(V * b->hist_pitch * 4) : 0;
+  const size_t o_hlen = o; o += (b->hist && b->hist_len) ? al(V * 4) : 0;
+  const size_t o_mt = o;   o += b->metric_type ? al(V) : 0;
+  FM_CK(c, c->in[0].reserve(o));
+  const size_t o_svc = al(G * sizeof(fm_series_rec));
+  FM_CK(c, c->out[0].reserve(o_svc + al(V * sizeof(fm_rollup_rec))));
+  char* din = static_cast<char*>(c->in[0].p);
+  char* dout = static_cast<char*>(c->out[0].p);
+  uint64_t h2d = 0;
+  auto up = [&](size_t off, const void* src, size_t bytes) -> cudaError_t {
+    h2d += bytes;
+    return cudaMemcpyAsync(din + off, src, bytes, cudaMemcpyHostToDevice, c->stream);
+  };
+  FM_CK(c, up(o_off, b->group_offsets, (V + 1) * 4));
+  if (G) FM_CK(c, up(o_cur, b->cur, G * b->cur_pitch * 4));
+  if (b->cur_len && G) FM_CK(c, up(o_clen, b->cur_len, G * 4));
+  if (b->hist && V) FM_CK(c, up(o_hist, b->hist, V * b->hist_pitch * 4));
+  if (b->hist && b->hist_len && V) FM_CK(c, up(o_hlen, b->hist_len, V * 4));
+  if (b->metric_type && V) FM_CK(c, up(o_mt, b->metric_type, V));
+  fm_group_batch db = *b;
+  db.group_offsets = reinterpret_cast<const uint32_t*>(din + o_off);
+  db.cur = reinterpret_cast<const float*>(din + o_cur);
+  db.cur_len = b->cur_len ? reinterpret_cast<const uint32_t*>(din + o_clen) : nullptr;
+  db.hist = b->hist ? reinterpret_cast<const float*>(din + o_hist) : nullptr;
+  db.hist_len = (b->hist && b->hist_len) ? reinterpret_cast<const uint32_t*>(din + o_hlen) : nullptr;
+  db.metric_type = b->metric_type ? reinterpret_cast<const uint8_t*>(din + o_mt) : nullptr;
+  fm_timing t; memset(&t, 0, sizeof(t));
+  int32_t rc = fm_score_groups_device(c, &db, reinterpret_cast<fm_series_rec*>(dout),
+                                      out_svc ? reinterpret_cast<fm_rollup_rec*>(dout + o_svc) : nullptr, &t);
+  if (rc != FM_OK) return rc;
+  if (G) FM_CK(c, cudaMemcpyAsync(out, dout, G * sizeof(fm_series_rec), cudaMemcpyDeviceToHost, c->stream));
+  if (out_svc && V) FM_CK(c, cudaMemcpyAsync(out_svc, dout + o_svc, V * sizeof(fm_rollup_rec), cudaMemcpyDeviceToHost, c->stream));
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  if (timing) {
+    *timing = t;
+    timing->h2d_bytes = h2d;
+    timing->d2h_bytes = G * sizeof(fm_series_rec) + (out_svc ? V * sizeof(fm_rollup_rec) : 0);
+  }
+  return FM_OK;
+}
+
+// ---------------------------------------------------------------------------
+int32_t fm_rank_dump(fm_ctx* c, const float* cur, uint32_t n_cur, const float* base, uint32_t n_base,
+                     uint32_t* r2_out) {
+  if (!c) return FM_E_INVALID;
+  const uint32_t N = n_cur + n_base;
+  if (N == 0) return FM_OK;
+  if (!r2_out || (n_cur && !cur) || (n_base && !base)) return fail(c, FM_E_INVALID, "null pointer");
+  if (N > (1u << 20)) return fail(c, FM_E_UNSUPPORTED, "rank dump limited to 2^20 points");
+  FM_CK(c, cudaSetDevice(c->device));
+  const uint32_t cap = pow2_ceil(N, 64u);
+  auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
+  const size_t o_cur = 0, o_base = al((size_t)n_cur * 4 + 4), o_sorted = o_base + al((size_t)n_base * 4 + 4),
+               o_r2 = o_sorted + al((size_t)cap * 4);
+  FM_CK(c, c->misc.reserve(o_r2 + al((size_t)N * 4)));
+  char* d = static_cast<char*>(c->misc.p);
+  if (n_cur) FM_CK(c, cudaMemcpyAsync(d + o_cur, cur, (size_t)n_cur * 4, cudaMemcpyHostToDevice, c->stream));
+  if (n_base) FM_CK(c, cudaMemcpyAsync(d + o_base, base, (size_t)n_base * 4, cudaMemcpyHostToDevice, c->stream));
+  fm_launch_rank_dump(reinterpret_cast<float*>(d + o_cur), n_cur, reinterpret_cast<float*>(d + o_base), n_base,
+                      reinterpret_cast<float*>(d + o_sorted), cap, reinterpret_cast<uint32_t*>(d + o_r2), c->stream);
+  FM_CK(c, cudaGetLastError());
+  FM_CK(c, cudaMemcpyAsync(r2_out, d + o_r2, (size_t)N * 4, cudaMemcpyDeviceToHost, c->stream));
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  return FM_OK;
+}
+
+int32_t fm_ma_window_series(fm_ctx* c, const float* x, uint32_t n, uint32_t w, uint32_t ddof,
+                            double* mean_out, double* sigma_out) {
+  if (!c) return FM_E_INVALID;
+  if (n == 0) return FM_OK;
+  if (!x || !mean_out || !sigma_out) return fail(c, FM_E_INVALID, "null pointer");
+  FM_CK(c, cudaSetDevice(c->device));
+  auto al = [](size_t v) { return (v + 255) & ~size_t(255); };
+  const size_t o_x = 0, o_p1 = al((size_t)n * 4), o_p2 = o_p1 + al((size_t)n * 8), o_m = o_p2 + al((size_t)n * 8),
+               o_s = o_m + al((size_t)n * 8);
+  FM_CK(c, c->misc.reserve(o_s + al((size_t)n * 8)));
+  char* d = static_cast<char*>(c->misc.p);
+  FM_CK(c, cudaMemcpyAsync(d + o_x, x, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+  fm_launch_ma_window(reinterpret_cast<float*>(d + o_x), n, w, ddof, reinterpret_cast<double*>(d + o_p1),
+                      reinterpret_cast<double*>(d + o_p2), reinterpret_cast<double*>(d + o_m),
+                      reinterpret_cast<double*>(d + o_s), c->stream);
+  FM_CK(c, cudaGetLastError());
+  FM_CK(c, cudaMemcpyAsync(mean_out, d + o_m, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+  FM_CK(c, cudaMemcpyAsync(sigma_out, d + o_s, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  return FM_OK;
+}
+
+// ---------------------------------------------------------------------------
+int32_t fm_synth_fill_device(fm_ctx* c, const fm_synth_desc* d, float* d_cur, float* d_base,
+                             float* d_hist, uint8_t* d_mt) {
+  if (!c) return FM_E_INVALID;
+  if (!d || d->struct_size != sizeof(fm_synth_desc)) return fail(c, FM_E_INVALID, "bad fm_synth_desc");
+  FM_CK(c, cudaSetDevice(c->device));
+  fm_launch_synth(*d, d_cur, d_base, d_hist, d_mt, c->stream);
+  FM_CK(c, cudaGetLastError());
+  return FM_OK;
+}
+
+int32_t fm_synth_fill_host(const fm_synth_desc* d, float* cur, float* base, float* hist,
+                           uint8_t* mt, uint32_t n_threads) {
+  if (!d || d->struct_size != sizeof(fm_synth_desc)) return FM_E_INVALID;
+  if (n_threads == 0) n_threads = std::max(1u, std::thread::hardware_concurrency());
+  n_threads = (uint32_t)std::min<uint64_t>(n_threads, std::max<uint64_t>(1, d->n_series));
+  auto work = [&](uint64_t lo, uint64_t hi) {
+    for (uint64_t r = lo; r < hi; ++r) {
+      const uint64_t id = d->row_ids ? d->row_ids[r] : d->first_series + r;
+      const fm_synth_series sp = fm_synth_series_params(d->seed, d->config, id, d->n_cur);
+      if (cur) for (uint32_t t = 0; t < d->cur_pitch; ++t) cur[r * d->cur_pitch + t] = t < d->n_cur ? fm_synth_sample(d->seed, &sp, id, FM_ROW_CUR, t) : 0.0f;
+      if (base) for (uint32_t t = 0; t < d->base_pitch; ++t) base[r * d->base_pitch + t] = t < d->n_base ? fm_synth_sample(d->seed, &sp, id, FM_ROW_BASE, t) : 0.0f;
+      if (hist) for (uint32_t t = 0; t < d->hist_pitch; ++t) hist[r * d->hist_pitch + t] = t < d->n_hist ? fm_synth_sample(d->seed, &sp, id, FM_ROW_HIST, t) : 0.0f;
+      if (mt) mt[r] = (uint8_t)sp.type;
+    }
+  };
+  std::vector<std::thread> th;
+  for (uint32_t t = 0; t < n_threads; ++t)
+    th.emplace_back(work, d->n_series * t / n_threads, d->n_series * (t + 1) / n_threads);
+  for (auto& x : th) x.join();
+  return FM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,401 @@
+// fm_device.cuh — device-side building blocks shared by the scoring kernels.
+//
+// Formula references (A.x) are DESIGN.md section 3; the reference text each one
+// implements is cited there and in include/foremast_cuda.h.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "fm_internal.h"
+
+#define FM_FULL 0xffffffffu
+
+// ------------------------------------------------------------------ PTX ----
+__device__ __forceinline__ uint32_t fm_smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void fm_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(fm_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fm_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fm_smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void fm_mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "FM_WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra FM_DONE_%=;\n"
+      "bra FM_WAIT_%=;\n"
+      "FM_DONE_%=:\n"
+      "}\n" ::"r"(fm_smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// 1-D bulk copy global -> shared through the TMA unit; completion on `bar`.
+// dst/src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void fm_bulk_g2s(void* dst, const void* src, uint32_t bytes,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(fm_smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(fm_smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void fm_fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void fm_fence_mbar_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ float4 fm_ldg_stream(const float4* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+
+// ------------------------------------------------------------- reductions --
+__device__ __forceinline__ double fm_warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FM_FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ long long fm_warp_sum(long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FM_FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ uint32_t fm_warp_sum(uint32_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FM_FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ uint32_t fm_warp_min(uint32_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(FM_FULL, v, o));
+  return v;
+}
+
+__device__ __forceinline__ uint32_t fm_pow2_ceil(uint32_t n, uint32_t lo) {
+  uint32_t p = lo;
+  while (p < n) p <<= 1;
+  return p;
+}
+
+// t^3 - t
+__device__ __forceinline__ long long fm_tie(uint32_t t) {
+  const long long x = (long long)t;
+  return x * x * x - x;
+}
+
+// ------------------------------------------------------------- moments -----
+// A.1: mean / sigma of a window with a pivot (the first sample) subtracted
+// before squaring so that sum(d^2) - sum(d)^2/n does not cancel
+// (SURVEY.md 7.2-4).  Partial sums are per lane; fm_moments_finish reduces.
+struct FmMom { double s1, s2; };
+
+__device__ __forceinline__ void fm_mom_add(FmMom& m, float x, double pivot) {
+  const double d = (double)x - pivot;
+  m.s1 += d;
+  m.s2 = fma(d, d, m.s2);
+}
+
+__device__ __forceinline__ void fm_moments_finish(FmMom m, double pivot, uint32_t n, uint32_t ddof,
+                                                  double& mean, double& sigma) {
+  const double s1 = fm_warp_sum(m.s1);
+  const double s2 = fm_warp_sum(m.s2);
+  const double dn = (double)n;
+  mean = pivot + s1 / dn;
+  double m2 = s2 - s1 * s1 / dn;
+  if (m2 < 0.0) m2 = 0.0;
+  sigma = (n > ddof) ? sqrt(m2 / (double)(n - ddof)) : 0.0;
+}
+
+// whole-warp moments over a GLOBAL row (16-byte aligned start), streaming loads
+__device__ __forceinline__ void fm_moments_global(const float* __restrict__ x, uint32_t n,
+                                                  uint32_t ddof, int lane, double& mean,
+                                                  double& sigma) {
+  const double pivot = (double)__ldg(x);
+  FmMom m = {0.0, 0.0};
+  const uint32_t n4 = n >> 2;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
+  uint32_t i = lane;
+  for (; i + 96 < n4; i += 128) {  // 4 independent 16-byte loads in flight per lane
+    const float4 a = fm_ldg_stream(x4 + i), b = fm_ldg_stream(x4 + i + 32),
+                 c = fm_ldg_stream(x4 + i + 64), d = fm_ldg_stream(x4 + i + 96);
+    fm_mom_add(m, a.x, pivot); fm_mom_add(m, a.y, pivot); fm_mom_add(m, a.z, pivot); fm_mom_add(m, a.w, pivot);
+    fm_mom_add(m, b.x, pivot); fm_mom_add(m, b.y, pivot); fm_mom_add(m, b.z, pivot); fm_mom_add(m, b.w, pivot);
+    fm_mom_add(m, c.x, pivot); fm_mom_add(m, c.y, pivot); fm_mom_add(m, c.z, pivot); fm_mom_add(m, c.w, pivot);
+    fm_mom_add(m, d.x, pivot); fm_mom_add(m, d.y, pivot); fm_mom_add(m, d.z, pivot); fm_mom_add(m, d.w, pivot);
+  }
+  for (; i < n4; i += 32) {
+    const float4 a = fm_ldg_stream(x4 + i);
+    fm_mom_add(m, a.x, pivot); fm_mom_add(m, a.y, pivot); fm_mom_add(m, a.z, pivot); fm_mom_add(m, a.w, pivot);
+  }
+  const uint32_t t = (n4 << 2) + lane;
+  if (t < n) fm_mom_add(m, __ldg(x + t), pivot);
+  fm_moments_finish(m, pivot, n, ddof, mean, sigma);
+}
+
+// whole-warp moments over an arbitrarily aligned row (shared or global), scalar loads
+__device__ __forceinline__ void fm_moments_any(const float* x, uint32_t n, uint32_t ddof, int lane,
+                                               double& mean, double& sigma) {
+  const double pivot = (double)x[0];
+  FmMom m = {0.0, 0.0};
+  for (uint32_t i = lane; i < n; i += 32) fm_mom_add(m, x[i], pivot);
+  fm_moments_finish(m, pivot, n, ddof, mean, sigma);
+}
+
+// Exponential / double exponential smoothing (design.md:60-66): a sequential
+// recurrence, evaluated by one lane and broadcast.
+__device__ __forceinline__ void fm_model_smoothing(const fm_global_params& g, const float* x,
+                                                   uint32_t n, int lane, double& mean,
+                                                   double& sigma) {
+  double mu = 0.0, sg = 0.0;
+  if (lane == 0) {
+    const double a = g.smooth_alpha, b = g.smooth_beta;
+    const bool dbl = g.ma_mode == FM_MODEL_DOUBLE_EXP;
+    double level = (double)x[0], trend = 0.0, sse = 0.0;
+    if (dbl && n > 1) trend = (double)x[1] - (double)x[0];
+    uint32_t m = 0;
+    for (uint32_t t = 1; t < n; ++t) {
+      const double f = __dadd_rn(level, dbl ? trend : 0.0);
+      const double e = __dsub_rn((double)x[t], f);
+      sse = __dadd_rn(sse, __dmul_rn(e, e));
+      ++m;
+      const double nl = __dadd_rn(f, __dmul_rn(a, e));
+      if (dbl) trend = __dadd_rn(trend, __dmul_rn(b, __dsub_rn(__dsub_rn(nl, level), trend)));
+      level = nl;
+    }
+    mu = __dadd_rn(level, dbl ? trend : 0.0);
+    sg = (m > g.ddof) ? sqrt(sse / (double)(m - g.ddof)) : 0.0;
+  }
+  mean = __shfl_sync(FM_FULL, mu, 0);
+  sigma = __shfl_sync(FM_FULL, sg, 0);
+}
+
+// a2: model window -> (mean, sigma).  `x` global or shared; `vec_ok` = row is a
+// 16-byte aligned global row.  Returns false when the window is too short.
+__device__ __forceinline__ bool fm_model(const fm_global_params& g, const float* x, uint32_t n,
+                                         bool vec_ok, int lane, double& mean, double& sigma) {
+  uint32_t need = max(g.min_hist_points, g.ddof + 1u);
+  mean = 0.0; sigma = 0.0;
+  if (x == nullptr) return false;
+  if (g.ma_mode == FM_MA_WINDOW) {
+    const uint32_t w = g.ma_window;
+    need = max(need, w);
+    if (n < need || w == 0) return false;
+    fm_moments_any(x + (n - w), w, g.ddof, lane, mean, sigma);
+    return true;
+  }
+  if (n < need) return false;
+  if (g.ma_mode == FM_MODEL_EWMA || g.ma_mode == FM_MODEL_DOUBLE_EXP) {
+    fm_model_smoothing(g, x, n, lane, mean, sigma);
+    return true;
+  }
+  if (vec_ok) fm_moments_global(x, n, g.ddof, lane, mean, sigma);
+  else fm_moments_any(x, n, g.ddof, lane, mean, sigma);
+  return true;
+}
+
+// ------------------------------------------------------- sort and search ---
+// Warp-level bitonic sort of n2 (power of two >= 64) keys in shared memory.
+template <typename T>
+__device__ __forceinline__ void fm_warp_bitonic(T* s, uint32_t n2, int lane) {
+  const uint32_t half = n2 >> 1;
+  for (uint32_t k = 2; k <= n2; k <<= 1) {
+    for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+      for (uint32_t i = lane; i < half; i += 32) {
+        const uint32_t a = ((i & ~(j - 1)) << 1) | (i & (j - 1));
+        const uint32_t b = a | j;
+        const bool up = (a & k) == 0;
+        const T x = s[a], y = s[b];
+        if ((x > y) == up) { s[a] = y; s[b] = x; }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ uint32_t fm_lower_bound(const T* a, uint32_t n, T x) {
+  uint32_t lo = 0, len = n;
+  while (len) {
+    const uint32_t h = len >> 1;
+    if (a[lo + h] < x) { lo += h + 1; len -= h + 1; } else len = h;
+  }
+  return lo;
+}
+template <typename T>
+__device__ __forceinline__ uint32_t fm_upper_bound(const T* a, uint32_t n, T x) {
+  uint32_t lo = 0, len = n;
+  while (len) {
+    const uint32_t h = len >> 1;
+    if (!(x < a[lo + h])) { lo += h + 1; len -= h + 1; } else len = h;
+  }
+  return lo;
+}
+
+// A.3: sum over tie runs of (t^3 - t) of a sorted array (per-lane partial).
+template <typename T>
+__device__ __forceinline__ long long fm_tie_term_sorted(const T* a, uint32_t lo, uint32_t n,
+                                                        int lane) {
+  long long t = 0;
+  for (uint32_t p = lo + lane; p < n; p += 32) {
+    const T v = a[p];
+    const bool start = (p == lo) || (a[p - 1] != v);
+    if (start && p + 1 < n && a[p + 1] == v) t += fm_tie(fm_upper_bound(a, n, v) - p);
+  }
+  return t;
+}
+
+// ----------------------------------------------------------- p-values ------
+struct FmTest { bool run; bool degenerate; double stat; double p; };
+
+// A.4 Mann-Whitney (normal approximation, tie-corrected, continuity optional)
+__device__ __forceinline__ FmTest fm_mann_whitney(long long r2_cur, long long T, uint32_t n1,
+                                                  uint32_t n2, uint32_t cc) {
+  FmTest t = {true, false, 0.0, 1.0};
+  const double N = (double)n1 + (double)n2;
+  const double u1 = 0.5 * (double)(r2_cur - (long long)n1 * ((long long)n1 + 1));
+  const double u2 = (double)n1 * (double)n2 - u1;
+  const double u = u1 > u2 ? u1 : u2;
+  const double mu = 0.5 * (double)n1 * (double)n2;
+  const double var = ((double)n1 * (double)n2 / 12.0) * ((N + 1.0) - (double)T / (N * (N - 1.0)));
+  t.stat = u1;
+  if (!(var > 0.0)) { t.degenerate = true; return t; }
+  const double z = (u - mu - (cc ? 0.5 : 0.0)) / sqrt(var);
+  const double p = erfc(z / 1.4142135623730951);
+  t.p = p > 1.0 ? 1.0 : p;
+  return t;
+}
+
+__device__ __forceinline__ FmTest fm_wilcoxon(long long w2p, long long w2m, long long T,
+                                              uint32_t np, uint32_t cc) {
+  FmTest t = {true, false, 0.0, 1.0};
+  const double w = 0.5 * (double)(w2p < w2m ? w2p : w2m);
+  const double n = (double)np;
+  const double mu = n * (n + 1.0) / 4.0;
+  const double var = n * (n + 1.0) * (2.0 * n + 1.0) / 24.0 - (double)T / 48.0;
+  t.stat = w;
+  if (!(var > 0.0)) { t.degenerate = true; return t; }
+  double num = w - mu;
+  if (cc && num != 0.0) num += 0.5;
+  const double z = num / sqrt(var);
+  const double p = erfc(fabs(z) / 1.4142135623730951);
+  t.p = p > 1.0 ? 1.0 : p;
+  return t;
+}
+
+// A.5 chi-square survival, integer dof, closed form
+__device__ __forceinline__ double fm_chi2_sf(double x, uint32_t dof) {
+  if (!(x > 0.0) || dof == 0) return 1.0;
+  const double hx = 0.5 * x;
+  const double e = exp(-hx);
+  const uint32_t m = dof >> 1;
+  if ((dof & 1u) == 0u) {
+    double term = 1.0, sum = 1.0;
+    for (uint32_t j = 1; j < m; ++j) { term *= hx / (double)j; sum += term; }
+    return e * sum;
+  }
+  double q = erfc(sqrt(hx));
+  if (m > 0) {
+    double term = 1.0, sum = 1.0;
+    for (uint32_t j = 2; j <= m; ++j) { term *= x / (double)(2 * j - 1); sum += term; }
+    q += e * sqrt(2.0 * x / 3.14159265358979323846) * sum;
+  }
+  return q;
+}
+
+// Kruskal-Wallis from H0 pieces: s = sum R_g^2 / n_g
+__device__ __forceinline__ FmTest fm_kruskal(double s, double N, long long T, uint32_t K) {
+  FmTest t = {true, false, 0.0, 1.0};
+  const double h0 = 12.0 / (N * (N + 1.0)) * s - 3.0 * (N + 1.0);
+  const double c = 1.0 - (double)T / (N * N * N - N);
+  if (!(c > 0.0)) { t.degenerate = true; return t; }
+  t.stat = h0 / c;
+  t.p = fm_chi2_sf(t.stat, K - 1);
+  return t;
+}
+
+__device__ __forceinline__ bool fm_mode_has(uint32_t mode, uint32_t test) {
+  return mode == test || mode == FM_PW_ALL || mode == FM_PW_ANY;
+}
+
+// A.6
+__device__ __forceinline__ bool fm_decide(uint32_t mode, double alpha, const FmTest* t, int n,
+                                          bool& skipped) {
+  int ne = 0; bool any = false, all = true;
+  for (int i = 0; i < n; ++i) {
+    if (!t[i].run || t[i].degenerate) continue;
+    ++ne;
+    const bool d = t[i].p < alpha;
+    any |= d; all &= d;
+  }
+  skipped = (ne == 0);
+  if (ne == 0) return false;
+  return mode == FM_PW_ALL ? all : any;
+}
+
+// A.7 + A.8: bounds, anomalous points of the current row (shared or global),
+// verdict.  Whole warp; fills the threshold part of `rec` (uniform).
+__device__ __forceinline__ void fm_threshold(const fm_global_params& g, const fm_type_params& tp,
+                                             bool differ, const float* cur, uint32_t n_cur,
+                                             int lane, fm_series_rec& rec) {
+  const double k = differ ? tp.k_low : tp.k;
+  const double up = __dadd_rn(rec.mean, __dmul_rn(k, rec.sigma));
+  double lo = __dsub_rn(rec.mean, __dmul_rn(k, rec.sigma));
+  if (lo < tp.min_lower_bound) lo = tp.min_lower_bound;
+  rec.upper = up; rec.lower = lo;
+  uint32_t cnt = 0, first = 0xFFFFFFFFu;
+  uint64_t mask = 0;
+  for (uint32_t i0 = 0; i0 < n_cur; i0 += 32) {
+    const uint32_t i = i0 + lane;
+    bool a = false;
+    if (i < n_cur) {
+      const double x = (double)cur[i];
+      a = ((tp.bound_mask & 1u) && x > up) || ((tp.bound_mask & 2u) && x < lo);
+    }
+    const uint32_t b = __ballot_sync(FM_FULL, a);
+    if (b) {
+      if (first == 0xFFFFFFFFu) first = i0 + (uint32_t)__ffs((int)b) - 1u;
+      cnt += (uint32_t)__popc(b);
+      if (i0 < 64) mask |= (uint64_t)b << i0;
+    }
+  }
+  rec.n_anom = cnt;
+  rec.first_idx = (uint16_t)(first == 0xFFFFFFFFu ? 0xFFFFu : (first < 0xFFFFu ? first : 0xFFFEu));
+  rec.anom_mask = mask;
+  rec.verdict = (cnt >= g.min_anomaly_points && cnt > 0) ? FM_UNHEALTHY : FM_HEALTHY;
+}
+
+__device__ __forceinline__ void fm_rec_init(fm_series_rec& r) {
+  r.mean = r.sigma = r.upper = r.lower = 0.0;
+  r.u1 = 0.0; r.p_u = 1.0; r.w = 0.0; r.p_w = 1.0; r.h = 0.0; r.p_h = 1.0;
+  r.n_anom = 0; r.first_idx = 0xFFFFu; r.verdict = FM_HEALTHY; r.status = 0; r.anom_mask = 0;
+}
+
+// One lane writes the record (full or compact).
+__device__ __forceinline__ void fm_write_record(void* out, uint64_t s, uint32_t kind,
+                                                const fm_series_rec& r) {
+  if (kind == FM_REC_COMPACT) {
+    fm_compact_rec c;
+    c.anom_mask = r.anom_mask; c.n_anom = r.n_anom; c.verdict = r.verdict; c.status = r.status;
+    c.first_idx = r.first_idx;
+    reinterpret_cast<uint4*>(out)[s] = *reinterpret_cast<const uint4*>(&c);
+  } else {
+    reinterpret_cast<fm_series_rec*>(out)[s] = r;
+  }
+}
+
+// Fused roll-up (a9): the per-API counters live in the output records.
+__device__ __forceinline__ void fm_rollup_add(fm_rollup_rec* api, uint32_t id, uint32_t verdict) {
+  atomicAdd(&api[id].n_children, 1u);
+  if (verdict == FM_UNHEALTHY) atomicAdd(&api[id].n_unhealthy, 1u);
+  if (verdict == FM_UNKNOWN) atomicAdd(&api[id].n_unknown, 1u);
+}

@@ -1,0 +1,69 @@
+// fm_internal.h — shared between the host API (fm_api.cu) and the kernels.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/foremast_cuda.h"
+
+// Parameters as the kernels see them (one device copy per ctx).
+struct FmParamsDev {
+  fm_global_params g;
+  uint32_t n_types;
+  uint32_t pad;
+  fm_type_params types[FM_MAX_TYPES];
+};
+
+// Arguments of the per-series scoring kernels.  Pointers are device pointers.
+struct FmKArgs {
+  const float* cur;  const uint32_t* cur_len;  uint32_t n_cur,  cur_pitch;
+  const float* base; const uint32_t* base_len; uint32_t n_base, base_pitch;
+  const float* hist; const uint32_t* hist_len; uint32_t n_hist, hist_pitch;
+  const uint8_t* metric_type;
+  const uint32_t* api_id;
+  uint64_t n_series;
+  void* out;               // fm_series_rec[] or fm_compact_rec[]
+  fm_rank_aux* aux;        // optional
+  fm_rollup_rec* api;      // optional: roll-up counters are accumulated in place
+  const FmParamsDev* P;
+  uint32_t record_kind;
+  uint32_t strategy;
+  // per-warp shared-memory layout, in elements
+  uint32_t cur_cap;        // floats, raw current row (multiple of 4)
+  uint32_t cs_cap;         // floats, sorted current row (power of two >= 32)
+  uint32_t base_cap;       // floats, baseline row, sorted in place (power of two >= 32, or 0)
+  uint32_t wx_cap;         // doubles, Wilcoxon |d| keys (power of two >= 32, or 0)
+  uint32_t wx_n;           // doubles, raw differences (max pairs)
+  uint32_t n_stages;       // 1 or 2 staging buffers per warp
+  uint32_t warp_bytes;     // bytes of shared memory per warp
+};
+
+struct FmGArgs {
+  const uint32_t* group_offsets;
+  const float* cur;  const uint32_t* cur_len;  uint32_t n_cur,  cur_pitch;
+  const float* hist; const uint32_t* hist_len; uint32_t n_hist, hist_pitch;
+  const uint8_t* metric_type;
+  uint64_t n_services;
+  fm_series_rec* out;
+  fm_rollup_rec* svc;      // optional
+  const FmParamsDev* P;
+  uint32_t pool_cap;       // floats: pooled sample, sorted (power of two)
+  uint32_t raw_cap;        // floats: pooled sample in group order
+  uint32_t warp_bytes;
+};
+
+// launchers (fm_kernels.cu); each returns the number of kernels launched
+int fm_launch_score(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st);
+int fm_launch_groups(const FmGArgs& a, int warps_per_cta, int grid, cudaStream_t st);
+int fm_launch_rollup_finalize(fm_rollup_rec* api, uint32_t n_apis, const uint32_t* api_service,
+                              fm_rollup_rec* svc, uint32_t n_services, cudaStream_t st);
+int fm_launch_rollup_finalize_one(fm_rollup_rec* recs, uint64_t n, cudaStream_t st);
+int fm_launch_rank_dump(const float* d_cur, uint32_t n_cur, const float* d_base, uint32_t n_base,
+                        float* d_sorted /* pow2 scratch */, uint32_t cap, uint32_t* d_r2,
+                        cudaStream_t st);
+int fm_launch_ma_window(const float* d_x, uint32_t n, uint32_t w, uint32_t ddof, double* d_p1,
+                        double* d_p2, double* d_mean, double* d_sigma, cudaStream_t st);
+int fm_launch_synth(const fm_synth_desc& d, float* cur, float* base, float* hist, uint8_t* mt,
+                    cudaStream_t st);
+
+cudaError_t fm_score_smem_attr(int bytes);
+cudaError_t fm_groups_smem_attr(int bytes);

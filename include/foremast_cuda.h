@@ -207,10 +207,12 @@ typedef struct {
 } fm_group_batch;
 
 typedef struct {
-  float    kernel_ms;      /* device time of the scoring launches (CUDA events on the ctx stream) */
-  uint32_t launches;       /* kernels launched by this call                                        */
-  float    h2d_ms, d2h_ms; /* fm_score_batch only: copy engine time, 0 otherwise                  */
-  uint64_t h2d_bytes, d2h_bytes;
+  float    kernel_ms;      /* device time of all launches of the call (CUDA events on the ctx stream) */
+  uint32_t launches;       /* kernels launched by this call                                            */
+  float    h2d_ms, d2h_ms; /* reserved (0)                                                             */
+  uint64_t h2d_bytes, d2h_bytes; /* fm_score_batch / fm_score_groups: bytes copied each way           */
+  float    main_kernel_ms; /* device time of the scoring kernel alone (roofline numerator's clock)    */
+  uint32_t reserved;
 } fm_timing;
 
 /* Synthetic workload descriptor (generator: include/fm_synth.h). */
@@ -222,12 +224,21 @@ typedef struct {
   uint64_t n_series;
   uint32_t n_cur, n_base, n_hist;
   uint32_t cur_pitch, base_pitch, hist_pitch;
+  const uint64_t* row_ids; /* optional [n_series] global id per row (device pointer for the
+                              device variant); NULL: id = first_series + row.  Config 4 uses
+                              id = (service << 4) | group. */
 } fm_synth_desc;
 
 /* ------------------------------------------------------------------------ */
 
 /* (major << 16) | minor. */
 int32_t fm_version(void);
+
+/* sizeof() of the ABI structs as compiled, for bindings to verify their mirror:
+ * 0 fm_global_params, 1 fm_type_params, 2 fm_batch, 3 fm_group_batch,
+ * 4 fm_series_rec, 5 fm_compact_rec, 6 fm_rank_aux, 7 fm_rollup_rec,
+ * 8 fm_timing, 9 fm_synth_desc; 0 for an unknown id. */
+uint32_t fm_sizeof(uint32_t which);
 
 /* Number of usable CUDA devices (0 and FM_OK when none). */
 int32_t fm_device_count(int32_t* out);

@@ -1,0 +1,300 @@
+"""GPU parity: libforemast_cuda.so (through the C ABI) against the CPU oracle on
+identical inputs.  Sizes are chosen so the oracle finishes in seconds; the
+full-size BASELINE shapes are covered by tests/test_gpu_fullsize.py.
+"""
+import copy
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from foremast_1_b200 import _abi as A
+from foremast_1_b200.engine import Context, synth_desc, synth_host
+from parity import assert_records_match, bound_masks
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = Context(0)
+    yield c
+    c.close()
+
+
+def params(**kw):
+    g, table = A.default_params()
+    for k, v in kw.items():
+        setattr(g, k, v)
+    return g, table
+
+
+def both(ctx, g, table, cur, base=None, hist=None, **kw):
+    ctx.set_params(g, table)
+    out = ctx.score(cur, base, hist, want_aux=True, **kw)
+    ora = O.score_batch(g, table, out["batch"], n_threads=8)
+    b = out["batch"]
+    S = int(b.n_series)
+    curm = np.ctypeslib.as_array(C.cast(b.cur, C.POINTER(C.c_float)), shape=(S, b.cur_pitch)) if S else np.zeros((0, 4), np.float32)
+    cl = kw.get("cur_len")
+    listed = assert_records_match(out["rec"], ora["rec"], curm[:, : b.n_cur], cl,
+                                  bound_masks(table, kw.get("metric_type"), S),
+                                  out["aux"], ora["aux"])
+    if out["api"] is not None:
+        assert (out["api"] == ora["api"]).all()
+    if out["svc"] is not None:
+        assert (out["svc"] == ora["svc"]).all()
+    return out, ora, listed
+
+
+def test_config1_single_job(ctx):
+    """BASELINE configs[0]: 1 service x 4 metrics, 60 vs 1440, MA + Mann-Whitney."""
+    d = synth_desc(1, 4, 60, 1440, 0)
+    cur, base, _, mt = synth_host(d)
+    g, t = params(pairwise_mode=A.FM_PW_MANN_WHITE)
+    out, ora, _ = both(ctx, g, t, cur, base, metric_type=mt,
+                       api_id=np.zeros(4, np.uint32), api_service=np.zeros(1, np.uint32),
+                       n_apis=1, n_services=1)
+    assert (out["rec"]["status"] & A.FM_ST_MW_RUN).all()
+
+
+@pytest.mark.parametrize("mode", [A.FM_PW_ANY, A.FM_PW_ALL, A.FM_PW_MANN_WHITE, A.FM_PW_WILCOXON,
+                                  A.FM_PW_KRUSKAL, A.FM_PW_NONE])
+def test_config3_shape_modes(ctx, mode):
+    d = synth_desc(3, 3000, 60, 1440, 0)
+    cur, base, _, mt = synth_host(d)
+    g, t = params(pairwise_mode=mode)
+    out, ora, _ = both(ctx, g, t, cur, base, metric_type=mt)
+    # the synthetic mix must exercise both verdicts and the pairwise decision
+    if mode == A.FM_PW_ANY:
+        v = out["rec"]["verdict"]
+        assert (v == A.FM_UNHEALTHY).any() and (v == A.FM_HEALTHY).any()
+        assert (out["rec"]["status"] & A.FM_ST_DIFFER).any()
+
+
+def test_config2_shape_separate_hist(ctx):
+    d = synth_desc(2, 300, 60, 1440, 10080)
+    cur, base, hist, mt = synth_host(d)
+    g, t = params(pairwise_mode=A.FM_PW_MANN_WHITE)
+    both(ctx, g, t, cur, base, hist, metric_type=mt)
+
+
+def test_historical_strategy(ctx):
+    d = synth_desc(5, 2000, 60, 0, 480)
+    cur, _, hist, mt = synth_host(d)
+    g, t = params()
+    out, _, _ = both(ctx, g, t, cur, None, hist, strategy=A.FM_STRAT_HISTORICAL, metric_type=mt,
+                     record_kind=A.FM_REC_COMPACT)
+    out2, _, _ = both(ctx, g, t, cur, None, hist, strategy=A.FM_STRAT_HISTORICAL, metric_type=mt)
+    assert (out["rec"]["verdict"] == out2["rec"]["verdict"]).all()
+
+
+def test_ragged_and_empty_rows(ctx):
+    rng = np.random.default_rng(7)
+    S = 600
+    d = synth_desc(3, S, 60, 500, 0)
+    cur, base, _, mt = synth_host(d)
+    cl = rng.integers(0, 61, S).astype(np.uint32)
+    bl = rng.integers(0, 501, S).astype(np.uint32)
+    cl[:8] = [0, 1, 4, 5, 19, 20, 21, 60]
+    bl[:8] = [500, 0, 3, 9, 10, 19, 20, 500]
+    g, t = params()
+    out, _, _ = both(ctx, g, t, cur, base, cur_len=cl, base_len=bl, metric_type=mt)
+    r = out["rec"]
+    assert r["verdict"][0] == A.FM_UNKNOWN and (r["status"][0] & A.FM_ST_NO_CURRENT)
+    assert r["verdict"][1] == A.FM_UNKNOWN and (r["status"][1] & A.FM_ST_HIST_INSUFFICIENT)
+
+
+def test_heavy_ties_and_degenerate(ctx):
+    rng = np.random.default_rng(11)
+    S = 400
+    cur = rng.integers(0, 4, (S, 60)).astype(np.float32)
+    base = rng.integers(0, 4, (S, 1440)).astype(np.float32)
+    cur[0] = 1.0; base[0] = 1.0            # everything tied: degenerate, p = 1
+    cur[1] = 0.0; base[1] = 0.0
+    cur[2, ::2] = -0.0; cur[2, 1::2] = 0.0; base[2] = 0.0; base[2, ::3] = -0.0   # -0 == +0
+    cur[3] = base[3, :60]                  # all differences zero: Wilcoxon skipped
+    g, t = params()
+    out, _, _ = both(ctx, g, t, cur, base)
+    r = out["rec"]
+    assert r["p_u"][0] == 1.0 and (r["status"][0] & A.FM_ST_DEGENERATE)
+    assert r["p_u"][2] == 1.0
+    assert not (r["status"][3] & A.FM_ST_WX_RUN)
+
+
+def test_many_ties_medium_cardinality(ctx):
+    rng = np.random.default_rng(5)
+    S = 300
+    cur = (rng.integers(0, 300, (S, 64)) / 7.0).astype(np.float32)
+    base = (rng.integers(0, 300, (S, 1000)) / 7.0).astype(np.float32)
+    g, t = params()
+    both(ctx, g, t, cur, base)
+
+
+@pytest.mark.parametrize("nc,nb", [(1, 1), (5, 7), (20, 20), (33, 100), (64, 64), (65, 2047),
+                                   (128, 2048), (300, 3000), (1000, 1000), (60, 10080)])
+def test_shapes(ctx, nc, nb):
+    rng = np.random.default_rng(nc * 7919 + nb)
+    S = 64
+    cur = rng.normal(5, 1, (S, nc)).astype(np.float32)
+    base = rng.normal(5, 1, (S, nb)).astype(np.float32)
+    base[: S // 2] = np.round(base[: S // 2] * 4) / 4   # half the series tie heavily
+    cur[: S // 2] = np.round(cur[: S // 2] * 4) / 4
+    g, t = params(min_hist_points=1)
+    both(ctx, g, t, cur, base, metric_type=rng.integers(0, 6, S).astype(np.uint8))
+
+
+def test_param_variants(ctx):
+    d = synth_desc(3, 800, 60, 1440, 0)
+    cur, base, _, mt = synth_host(d)
+    for kw in (dict(ddof=1), dict(pair_rule=A.FM_PAIR_TAIL), dict(cc_mw=0, cc_wx=1),
+               dict(ma_mode=A.FM_MA_WINDOW, ma_window=120), dict(min_anomaly_points=3),
+               dict(alpha=0.5), dict(min_mw=61), dict(ma_mode=A.FM_MODEL_EWMA),
+               dict(ma_mode=A.FM_MODEL_DOUBLE_EXP)):
+        g, t = params(**kw)
+        both(ctx, g, t, cur, base, metric_type=mt)
+    g, t = params()
+    for i in range(len(t)):
+        t[i].bound_mask = 1 + (i % 3)
+        t[i].min_lower_bound = 0.25 * i
+        t[i].k = 1.5 + 0.5 * i
+        t[i].k_low = 1.0
+    both(ctx, g, t, cur, base, metric_type=mt)
+
+
+def test_memory_like_cancellation(ctx):
+    """mean ~1e9, sigma/mean ~1e-6: the pivoted moments must keep 1e-6 on sigma."""
+    rng = np.random.default_rng(3)
+    S = 200
+    base = (1.0e9 + rng.integers(-2000, 2000, (S, 1440)) * 64.0).astype(np.float32)
+    cur = (1.0e9 + rng.integers(-2000, 2000, (S, 60)) * 64.0).astype(np.float32)
+    base[0] = 1.0e9                       # zero variance
+    g, t = params()
+    both(ctx, g, t, cur, base, metric_type=np.full(S, 5, np.uint8))
+
+
+def test_rollup(ctx):
+    S = 4096
+    d = synth_desc(5, S, 60, 0, 240)
+    cur, _, hist, mt = synth_host(d)
+    api = (np.arange(S) // 4).astype(np.uint32)          # 4 metrics per API
+    svc = (np.arange(S // 4) // 8).astype(np.uint32)     # 8 APIs per service
+    cl = np.full(S, 60, np.uint32)
+    cl[:32] = 0                                          # one whole service unknown
+    g, t = params()
+    out, ora, _ = both(ctx, g, t, cur, None, hist, strategy=A.FM_STRAT_HISTORICAL, cur_len=cl,
+                       metric_type=mt, api_id=api, api_service=svc, n_apis=S // 4, n_services=S // 32)
+    assert out["svc"]["severity"][0] == A.FM_UNKNOWN
+    assert (out["svc"]["n_children"] == 8).all()
+    assert set(np.unique(out["svc"]["severity"])) >= {A.FM_HEALTHY, A.FM_UNHEALTHY}
+
+
+def test_multi_chunk_pipeline(ctx):
+    """More series than one host->device chunk: both staging slots get reused."""
+    S = 40000
+    d = synth_desc(3, S, 60, 1440, 0)
+    cur, base, _, mt = synth_host(d)
+    g, t = params(pairwise_mode=A.FM_PW_MANN_WHITE)
+    ctx.set_params(g, t)
+    out = ctx.score(cur, base, metric_type=mt, want_aux=True)
+    # oracle on a strided subset (full 40k would take a while on few cores)
+    idx = np.arange(0, S, 37)
+    sub = ctx.score(cur[idx], base[idx], metric_type=mt[idx], want_aux=True)
+    ora = O.score_batch(g, t, sub["batch"], n_threads=8)
+    assert_records_match(sub["rec"], ora["rec"], cur[idx][:, :60], None, bound_masks(t, mt[idx], idx.size),
+                         sub["aux"], ora["aux"])
+    assert (out["rec"][idx] == sub["rec"]).all()
+    assert (out["aux"][idx] == sub["aux"]).all()
+
+
+def test_groups_kruskal(ctx):
+    rng = np.random.default_rng(17)
+    V = 500
+    K = rng.integers(3, 9, V)
+    off = np.concatenate([[0], np.cumsum(K)]).astype(np.uint32)
+    G = int(off[-1])
+    ids = np.concatenate([(v << 4) + np.arange(K[v]) for v in range(V)]).astype(np.uint64)
+    d = synth_desc(4, G, 60, 0, 0, row_ids=ids.ctypes.data)
+    cur, _, _, _ = synth_host(d)
+    hids = (np.arange(V, dtype=np.uint64) << np.uint64(4))
+    dh = synth_desc(4, V, 60, 0, 1440, row_ids=hids.ctypes.data)
+    _, _, hist, mt = synth_host(dh)
+    # make a few services differ: shift one group
+    for v in range(0, V, 9):
+        cur[off[v]] += np.float32(1.0 / 60.0) * 3
+    cl = np.full(G, 60, np.uint32)
+    cl[off[1]] = 3          # a group below MIN_KRUSKAL_DATA_POINTS: test skipped for that service
+    cl[off[2]] = 0
+    g, t = params(pairwise_mode=A.FM_PW_KRUSKAL)
+    ctx.set_params(g, t)
+    out = ctx.score_groups(cur, off, hist, cur_len=cl, metric_type=mt)
+    ora = O.score_groups(g, t, out["batch"], n_threads=8)
+    gmt = np.repeat(mt, K)
+    assert_records_match(out["rec"], ora["rec"], cur[:, :60], cl, bound_masks(t, gmt, G))
+    assert (out["svc"] == ora["svc"]).all()
+    assert (out["rec"]["status"] & A.FM_ST_DIFFER).any()
+    assert (out["rec"]["status"][off[1]] & A.FM_ST_PAIRWISE_SKIPPED)
+
+
+def test_rank_dump(ctx):
+    rng = np.random.default_rng(2)
+    for nc, nb in [(5, 9), (60, 1440), (64, 64), (1, 0), (0, 3)]:
+        cur = np.round(rng.normal(0, 2, nc)).astype(np.float32)
+        base = np.round(rng.normal(0, 2, nb)).astype(np.float32)
+        assert (ctx.rank_dump(cur, base) == O.rank_dump(cur, base)).all()
+
+
+def test_ma_window_series(ctx):
+    rng = np.random.default_rng(4)
+    x = (1.0e6 + rng.normal(0, 30, 5000)).astype(np.float32)
+    for w, ddof in [(1, 0), (10, 0), (60, 1), (1440, 0), (5000, 1)]:
+        m, s = ctx.ma_window_series(x, w, ddof)
+        mo, so = O.ma_window_series(x, w, ddof)
+        assert np.array_equal(np.isnan(m), np.isnan(mo))
+        ok = ~np.isnan(mo)
+        assert np.allclose(m[ok], mo[ok], rtol=1e-6, atol=0)
+        assert np.allclose(s[ok], so[ok], rtol=1e-6, atol=1e-9)
+
+
+def test_synth_device_matches_host(ctx):
+    for cfg, nb, nh in [(3, 1440, 0), (2, 100, 300), (5, 0, 77)]:
+        S = 257
+        d = synth_desc(cfg, S, 60, nb, nh, first_series=12345)
+        cur, base, hist, mt = synth_host(d)
+        dc = ctx.dev_alloc(S * d.cur_pitch * 4)
+        db = ctx.dev_alloc(max(1, S * d.base_pitch * 4))
+        dh = ctx.dev_alloc(max(1, S * d.hist_pitch * 4))
+        dm = ctx.dev_alloc(S)
+        ctx.synth_device(d, dc, db if nb else None, dh if nh else None, dm)
+        ctx.sync()
+        gc = np.zeros_like(cur); ctx.d2h(gc, dc)
+        assert gc.tobytes() == cur.tobytes()
+        if nb:
+            gb = np.zeros_like(base); ctx.d2h(gb, db)
+            assert gb.tobytes() == base.tobytes()
+        if nh:
+            gh = np.zeros_like(hist); ctx.d2h(gh, dh)
+            assert gh.tobytes() == hist.tobytes()
+        gm = np.zeros_like(mt); ctx.d2h(gm, dm)
+        assert (gm == mt).all()
+        for p in (dc, db, dh, dm):
+            ctx.dev_free(p)
+
+
+def test_errors(ctx):
+    g, t = params()
+    ctx.set_params(g, t)
+    from foremast_1_b200._ffi import ForemastCudaError
+    with pytest.raises(ForemastCudaError) as e:
+        ctx.score(np.zeros((2, 5000), np.float32), np.zeros((2, 100), np.float32))
+    assert e.value.code == A.FM_E_UNSUPPORTED
+    g2 = copy.copy(g)
+    g2.ddof = 7
+    with pytest.raises(ForemastCudaError) as e:
+        ctx.set_params(g2, t)
+    assert e.value.code == A.FM_E_INVALID
+    # the ctx stays usable after an error
+    ctx.set_params(g, t)
+    out = ctx.score(np.ones((1, 8), np.float32), np.ones((1, 16), np.float32))
+    assert out["rec"]["verdict"][0] == A.FM_HEALTHY

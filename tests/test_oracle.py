@@ -1,0 +1,200 @@
+"""Pins the CPU oracle: hand-derived known answers, scipy (float64 inputs) as a
+second opinion, and the frozen golden fixtures under tests/golden/.
+
+The reference holds no implementation and no test vectors for this path
+("parity unpinned", oracle/fm_oracle.h), so these are the anchors.
+"""
+import json
+import os
+from fractions import Fraction
+
+import numpy as np
+import pytest
+from scipy import stats
+
+import oracle_lib as O
+from foremast_1_b200 import _abi as A
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def params(**kw):
+    g, t = A.default_params()
+    for k, v in kw.items():
+        setattr(g, k, v)
+    return g, t
+
+
+# ---------------------------------------------------------------- A.1 / A.2 --
+def test_moments_known_answer():
+    m, s = O.moments([2, 4, 4, 4, 5, 5, 7, 9], 0)
+    assert m == 5.0 and s == 2.0
+    m, s = O.moments([2, 4, 4, 4, 5, 5, 7, 9], 1)
+    assert m == 5.0 and s == pytest.approx(np.sqrt(32 / 7), rel=1e-15)
+    assert O.moments([3.5], 0) == (3.5, 0.0)
+    assert O.moments([3.5], 1) == (3.5, 0.0)
+
+
+def test_window_series_matches_numpy():
+    rng = np.random.default_rng(0)
+    x = rng.normal(10, 2, 300).astype(np.float32)
+    m, s = O.ma_window_series(x, 25, 0)
+    assert np.isnan(m[:24]).all() and not np.isnan(m[24:]).any()
+    for t in (24, 100, 299):
+        win = x[t - 24: t + 1].astype(np.float64)
+        assert m[t] == pytest.approx(win.mean(), rel=1e-14)
+        assert s[t] == pytest.approx(win.std(), rel=1e-12)
+
+
+# ---------------------------------------------------------------------- A.3 --
+def test_midranks_known_answer():
+    # sorted: 1 2 2 3 3 3 7 -> ranks 1, 2.5, 2.5, 5, 5, 5, 7
+    r2, T = O.midranks([3, 1, 2, 3, 2, 7, 3])
+    assert r2.tolist() == [10, 2, 5, 10, 5, 14, 10]
+    assert T == (2 ** 3 - 2) + (3 ** 3 - 3)
+    r2, T = O.midranks([0.0, -0.0, 0.0])      # -0 ties with +0
+    assert r2.tolist() == [4, 4, 4] and T == 24
+
+
+def test_midranks_vs_scipy_rankdata():
+    rng = np.random.default_rng(1)
+    for n in (1, 2, 17, 500):
+        v = np.round(rng.normal(0, 3, n))
+        r2, T = O.midranks(v)
+        assert np.array_equal(r2, (2 * stats.rankdata(v)).astype(np.uint32))
+        _, cnt = np.unique(v, return_counts=True)
+        assert T == int((cnt.astype(np.int64) ** 3 - cnt).sum())
+
+
+# ---------------------------------------------------------------------- A.4 --
+def exact_mwu(x, y):
+    """Mann-Whitney U1 and tie term by exact rational arithmetic (tiny inputs)."""
+    u = Fraction(0)
+    for a in x:
+        for b in y:
+            u += 1 if a > b else (Fraction(1, 2) if a == b else 0)
+    allv = list(x) + list(y)
+    T = sum(c ** 3 - c for c in (allv.count(v) for v in set(allv)))
+    return u, T
+
+
+def test_mann_whitney_hand_case():
+    x = np.array([1.0, 2.0, 2.0, 5.0] * 5, np.float32)
+    y = np.array([0.0, 2.0, 3.0, 3.0, 4.0] * 5, np.float32)
+    g, t = params(pairwise_mode=A.FM_PW_MANN_WHITE, min_hist_points=1)
+    rec, aux = O.score_series(g, t[0], A.FM_STRAT_CANARY, x, y)
+    u, T = exact_mwu(x.tolist(), y.tolist())
+    assert Fraction(rec["u1"]).limit_denominator(2) == u
+    assert aux["t_mw"] == T
+    n1, n2 = len(x), len(y)
+    assert aux["r2_cur"] == int(2 * u + n1 * (n1 + 1))
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_tests_vs_scipy(seed):
+    rng = np.random.default_rng(seed)
+    nc, nb = int(rng.integers(20, 80)), int(rng.integers(20, 400))
+    if seed % 2:
+        cur = rng.integers(0, 6, nc).astype(np.float32)
+        base = rng.integers(0, 6, nb).astype(np.float32)
+    else:
+        cur = rng.normal(0.3, 1, nc).astype(np.float32)
+        base = rng.normal(0, 1, nb).astype(np.float32)
+    g, t = params(pairwise_mode=A.FM_PW_ANY, min_hist_points=1)
+    rec, aux = O.score_series(g, t[0], A.FM_STRAT_CANARY, cur, base)
+    c64, b64 = cur.astype(np.float64), base.astype(np.float64)
+    r = stats.mannwhitneyu(c64, b64, use_continuity=True, alternative="two-sided", method="asymptotic")
+    assert rec["u1"] == r.statistic and rec["p_u"] == pytest.approx(r.pvalue, rel=1e-12)
+    n = min(nc, nb)
+    d = c64[:n] - b64[:n]
+    if (d != 0).sum() >= 20:
+        wx = stats.wilcoxon(c64[:n], b64[:n], zero_method="wilcox", correction=False, method="asymptotic")
+        assert rec["w"] == wx.statistic and rec["p_w"] == pytest.approx(wx.pvalue, rel=1e-12)
+    k = stats.kruskal(c64, b64)
+    assert rec["h"] == pytest.approx(k.statistic, rel=1e-12) and rec["p_h"] == pytest.approx(k.pvalue, rel=1e-10)
+
+
+def test_chi2_sf_vs_scipy():
+    for dof in range(1, 16):
+        for x in (1e-9, 0.3, 1.0, 5.5, 20.0, 80.0, 400.0):
+            assert O.chi2_sf(x, dof) == pytest.approx(stats.chi2.sf(x, dof), rel=1e-12, abs=1e-300)
+    assert O.chi2_sf(0.0, 3) == 1.0 and O.chi2_sf(-1.0, 2) == 1.0
+
+
+def test_degenerate_and_eligibility():
+    g, t = params(min_hist_points=1)
+    one = np.ones(30, np.float32)
+    rec, aux = O.score_series(g, t[0], A.FM_STRAT_CANARY, one, np.ones(100, np.float32))
+    assert rec["p_u"] == 1.0 and rec["p_h"] == 1.0 and rec["status"] & A.FM_ST_DEGENERATE
+    assert aux["n_wx"] == 0 and not (rec["status"] & A.FM_ST_WX_RUN)
+    assert rec["status"] & A.FM_ST_PAIRWISE_SKIPPED and not (rec["status"] & A.FM_ST_DIFFER)
+    # fewer points than MIN_MANN_WHITE / MIN_WILCOXON (20) but enough for Kruskal (5)
+    rng = np.random.default_rng(0)
+    rec, _ = O.score_series(g, t[0], A.FM_STRAT_CANARY, rng.normal(0, 1, 10), rng.normal(0, 1, 50))
+    assert not (rec["status"] & (A.FM_ST_MW_RUN | A.FM_ST_WX_RUN)) and rec["status"] & A.FM_ST_KW_RUN
+
+
+# ------------------------------------------------------------- A.6 .. A.8 ----
+def test_threshold_lowering_and_verdict():
+    rng = np.random.default_rng(3)
+    base = rng.normal(10, 1, 1440).astype(np.float32)
+    mu, sd = O.moments(base)
+    cur_same = rng.normal(10, 1, 60).astype(np.float32)
+    cur_same[5] = np.float32(mu + 1.5 * sd)       # inside k=2, outside k_low=1
+    g, t = params(pairwise_mode=A.FM_PW_MANN_WHITE)
+    rec, _ = O.score_series(g, t[1], A.FM_STRAT_CANARY, cur_same, base)
+    if not (rec["status"] & A.FM_ST_DIFFER):
+        assert rec["upper"] == pytest.approx(mu + 2 * sd, rel=1e-14)
+    cur_shift = (rng.normal(10, 1, 60) + 0.8).astype(np.float32)   # distributions differ -> k_low
+    rec, _ = O.score_series(g, t[1], A.FM_STRAT_CANARY, cur_shift, base)
+    assert rec["status"] & A.FM_ST_DIFFER and rec["upper"] == pytest.approx(mu + 1 * sd, rel=1e-14)
+    assert rec["verdict"] == A.FM_UNHEALTHY and rec["n_anom"] == int((cur_shift.astype(np.float64) > rec["upper"]).sum())
+    # bound mask 3 (latency): lower side too, floored by min_lower_bound
+    rec, _ = O.score_series(g, t[3], A.FM_STRAT_HISTORICAL, np.array([-5.0, 10.0], np.float32), None, base)
+    assert rec["lower"] == pytest.approx(mu - 10 * sd, rel=1e-12)
+    assert rec["n_anom"] == 1 and rec["first_idx"] == 0 and rec["anom_mask"] == 1
+    rec, _ = O.score_series(g, t[3], A.FM_STRAT_HISTORICAL, np.array([-5.0, 1.0], np.float32), None, base - 9)
+    assert rec["lower"] == 0.0 and rec["n_anom"] == 1          # floored by min_lower_bound = 0
+    # unknown: no current points / too little history (design.md:25)
+    rec, _ = O.score_series(g, t[0], A.FM_STRAT_HISTORICAL, np.zeros(0, np.float32), None, base)
+    assert rec["verdict"] == A.FM_UNKNOWN and rec["status"] & A.FM_ST_NO_CURRENT
+    rec, _ = O.score_series(g, t[0], A.FM_STRAT_HISTORICAL, cur_same, None, base[:5])
+    assert rec["verdict"] == A.FM_UNKNOWN and rec["status"] & A.FM_ST_HIST_INSUFFICIENT
+
+
+def test_demo_fixture_flags_the_two_spikes():
+    """examples/spring-boot-demo data1.txt (normal) vs data2.txt (two 40.x spikes):
+    with k = 2, upper bound only, exactly the two spikes are anomalous
+    (docs/guides/installation.md:84,126-134 describes the Unhealthy outcome)."""
+    with open(os.path.join(HERE, "golden", "demo_data.json")) as f:
+        d = json.load(f)
+    g, t = params(min_hist_points=10)
+    rec, _ = O.score_series(g, t[1], A.FM_STRAT_HISTORICAL, d["data2"], None, d["data1"])
+    spikes = [i for i, v in enumerate(d["data2"]) if v > 40]
+    assert len(spikes) == 2
+    assert rec["verdict"] == A.FM_UNHEALTHY and rec["n_anom"] == 2
+    assert rec["first_idx"] == spikes[0]
+    assert rec["anom_mask"] == sum(1 << i for i in spikes)
+
+
+# ------------------------------------------------------------------ A.9 ------
+def test_rollup_rule():
+    import ctypes as C
+    v = np.array([0, 0, 1, 2, 2, 2, 0, 2], np.uint8)
+    parent = np.array([0, 0, 0, 1, 1, 2, 2, 3], np.uint32)
+    out = np.zeros(5, A.ROLLUP_REC)
+    O.lib().fmo_rollup(C.c_void_p(v.ctypes.data), C.c_void_p(parent.ctypes.data), C.c_uint64(v.size),
+                       C.c_void_p(out.ctypes.data), C.c_uint32(5))
+    assert out["severity"].tolist() == [A.FM_UNHEALTHY, A.FM_UNKNOWN, A.FM_HEALTHY, A.FM_UNKNOWN, A.FM_HEALTHY]
+    assert out["n_children"].tolist() == [3, 2, 2, 1, 0]
+
+
+# ------------------------------------------------------------- golden files --
+def test_golden_records():
+    """Frozen oracle outputs on seeded synthetic batches (tests/golden/make_golden.py)."""
+    from make_golden import CASES, run_case
+    z = np.load(os.path.join(HERE, "golden", "oracle_records.npz"))
+    for name in CASES:
+        out = run_case(name)
+        for k, v in out.items():
+            assert v.tobytes() == z[f"{name}__{k}"].tobytes(), (name, k)
