@@ -1,0 +1,359 @@
+"""Host-side mirror of the brain's interface for the scoring path.
+
+The reference decouples the brain through the Elasticsearch document
+(foremast-service/pkg/models/models.go:83-101): the service writes
+status "initial" plus three config strings, the brain fetches the series,
+scores them and writes status / reason / anomalyInfo back
+(docs/guides/design.md:35-49).  Everything here is host logic (string
+parsing, JSON decoding, document bookkeeping); every number comes from
+libforemast_cuda.so through engine.Context.
+
+  parse_config          inverse of convertMetricQuerys (cmd/manager/main.go:28-74)
+  params_from_env       the env block of deploy/foremast/3_brain/foremast-brain.yaml:21-81
+  decode_query_range    Prometheus query_range JSON -> (timestamps, values) rows
+                        (response shape: foremast-browser/src/App.js:278-292)
+  score_documents       one poll of "initial" documents -> one coalesced batch ->
+                        status / reason / anomalyInfo per document
+  BrainWorker           poll / claim / takeover loop over a document store
+                        (pkg/search/elasticsearchstore.go:124-149; design.md:37-43)
+"""
+import json
+import time
+import urllib.request
+
+import numpy as np
+
+from . import _abi as A
+
+# foremast-service/cmd/manager/main.go:28,31
+CONFIG_SEPARATOR = " ||"
+KV_SEPARATOR = "== "
+
+# internal document statuses (pkg/converter/converter.go:11-30)
+ST_INITIAL = "initial"
+ST_PRE_INPROGRESS = "preprocess_inprogress"
+ST_PRE_COMPLETED = "preprocess_completed"
+ST_PRE_FAILED = "preprocess_failed"
+ST_POST_INPROGRESS = "postprocess_inprogress"
+ST_HEALTH = "completed_health"
+ST_UNHEALTH = "completed_unhealth"
+ST_UNKNOWN = "completed_unknown"
+ST_ABORT = "abort"
+
+VERDICT_STATUS = {A.FM_HEALTHY: ST_HEALTH, A.FM_UNHEALTHY: ST_UNHEALTH, A.FM_UNKNOWN: ST_UNKNOWN}
+
+# strategy spellings: this snapshot of the reference (metricsquery.go:17-19) and BASELINE.json
+CANARY_STRATEGIES = {"canary"}
+HISTORICAL_STRATEGIES = {"rollingupdate", "rollover", "continuous", "hpa"}
+
+
+def external_status(status):
+    """pkg/converter/converter.go:11-30 (what barrelman sees)."""
+    if status == ST_INITIAL:
+        return "new"
+    if status == ST_HEALTH:
+        return "success"
+    if status == ST_UNHEALTH:
+        return "anomaly"
+    if status in (ST_UNKNOWN, ST_PRE_FAILED, ST_ABORT):
+        return "abort"
+    return "inprogress"
+
+
+def parse_config(s):
+    """'alias== url ||alias2== url2' -> {alias: url} (main.go:49-74)."""
+    out = {}
+    if not s:
+        return out
+    for part in s.split(CONFIG_SEPARATOR):
+        if not part.strip():
+            continue
+        if KV_SEPARATOR not in part:
+            raise ValueError(f"config entry without '{KV_SEPARATOR}': {part!r}")
+        k, v = part.split(KV_SEPARATOR, 1)
+        out[k.strip()] = v.strip()
+    return out
+
+
+def format_config(d):
+    """The service-side formatting, for tests and fakes (main.go:49-74)."""
+    return CONFIG_SEPARATOR.join(f"{k}{KV_SEPARATOR}{v}" for k, v in d.items())
+
+
+_PAIRWISE = {"ALL": A.FM_PW_ALL, "ANY": A.FM_PW_ANY, "MANN_WHITE": A.FM_PW_MANN_WHITE,
+             "WILCOXON": A.FM_PW_WILCOXON, "KRUSKAL": A.FM_PW_KRUSKAL, "NONE": A.FM_PW_NONE}
+_ALGORITHMS = {"moving_average_all": A.FM_MA_ALL, "moving_average": A.FM_MA_WINDOW,
+               "exponential_smoothing": A.FM_MODEL_EWMA,
+               "double_exponential_smoothing": A.FM_MODEL_DOUBLE_EXP}
+
+
+def params_from_env(env):
+    """Env knobs of the brain deployment -> (GlobalParams, TypeParams table, {type name: id}).
+
+    Names and the indexed per-metric-type override scheme
+    (metric_type{i}/threshold{i}/bound{i}/min_lower_bound{i},
+    metric_type_threshold_count) follow foremast-brain.yaml:24-79 and
+    foremast-brain/README.md:22-38.  Index 0 of the table is the default row.
+    """
+    g, _ = A.default_params()
+    algo = env.get("ML_ALGORITHM", "moving_average_all")
+    if algo not in _ALGORITHMS:
+        raise ValueError(f"unsupported ML_ALGORITHM {algo!r}")
+    g.ma_mode = _ALGORITHMS[algo]
+    g.ma_window = int(env.get("ML_MOVING_AVERAGE_WINDOW", "0"))
+    g.min_hist_points = int(env.get("MIN_HISTORICAL_DATA_POINT_TO_MEASURE", "10"))
+    pw = env.get("ML_PAIRWISE_ALGORITHM", "ANY").upper()
+    if pw not in _PAIRWISE:
+        raise ValueError(f"unsupported ML_PAIRWISE_ALGORITHM {pw!r}")
+    g.pairwise_mode = _PAIRWISE[pw]
+    g.alpha = float(env.get("ML_PAIRWISE_THRESHOLD", "0.05"))
+    g.min_mw = int(env.get("MIN_MANN_WHITE_DATA_POINTS", "20"))
+    g.min_wx = int(env.get("MIN_WILCOXON_DATA_POINTS", "20"))
+    g.min_kw = int(env.get("MIN_KRUSKAL_DATA_POINTS", "5"))
+    k0 = float(env.get("ML_THRESHOLD", env.get("threshold", "2.0")))
+    b0 = int(env.get("ML_BOUND", env.get("bound", "1")))
+    lo0 = float(env.get("min_lower_bound", "0"))
+    n = int(env.get("metric_type_threshold_count", "0"))
+    if n + 1 > A.FM_MAX_TYPES:
+        raise ValueError("too many metric types")
+    table = (A.TypeParams * (n + 1))()
+    names = {"default": 0}
+
+    def fill(row, k, b, lo):
+        if b not in (1, 2, 3):
+            raise ValueError(f"bound must be 1 (upper), 2 (lower) or 3 (both), got {b}")
+        row.k, row.k_low, row.min_lower_bound, row.bound_mask = k, 0.5 * k, lo, b
+
+    fill(table[0], k0, b0, lo0)
+    for i in range(n):
+        name = env.get(f"metric_type{i}")
+        if not name:
+            raise ValueError(f"metric_type{i} missing")
+        names[name] = i + 1
+        fill(table[i + 1], float(env.get(f"threshold{i}", k0)), int(env.get(f"bound{i}", b0)),
+             float(env.get(f"min_lower_bound{i}", lo0)))
+    return g, table, names
+
+
+def metric_type_id(alias, names):
+    """Metric alias -> row of the threshold table: exact name, else the longest
+    type name contained in the alias (aliases like 'error5xx', 'latency',
+    'namespace_app_per_pod:cpu_usage' ...)."""
+    if alias in names:
+        return names[alias]
+    a = alias.lower()
+    best, bl = 0, 0
+    for n, i in names.items():
+        if i and n.lower() in a and len(n) > bl:
+            best, bl = i, len(n)
+    return best
+
+
+def decode_query_range(payload):
+    """Prometheus query_range body -> list of (labels, ts int64[], values float32[]).
+
+    Shape: {"status":"success","data":{"result":[{"metric":{..},"values":[[ts,"v"],..]}]}}
+    (foremast-browser/src/App.js:278-292).  NaN / Inf samples (Prometheus gaps,
+    divisions by zero in recording rules) are dropped: the ABI wants NaN-free rows.
+    """
+    if isinstance(payload, (bytes, bytearray)):
+        payload = payload.decode("utf-8")
+    if isinstance(payload, str):
+        payload = json.loads(payload)
+    if isinstance(payload, str):          # the service's proxy double-encodes (App.js:281)
+        payload = json.loads(payload)
+    if payload.get("status", "success") != "success":
+        raise ValueError(f"query_range failed: {payload.get('error', payload.get('status'))}")
+    out = []
+    for r in payload.get("data", {}).get("result", []):
+        vals = r.get("values", [])
+        ts = np.fromiter((int(float(v[0])) for v in vals), dtype=np.int64, count=len(vals))
+        x = np.fromiter((float(v[1]) for v in vals), dtype=np.float64, count=len(vals))
+        keep = np.isfinite(x)
+        out.append((r.get("metric", {}), ts[keep], x[keep].astype(np.float32)))
+    return out
+
+
+def merge_series(results):
+    """Several result series of one query (one per pod) -> one time-ordered row,
+    the way a single metric alias is judged as one sample set."""
+    if not results:
+        return np.zeros(0, np.int64), np.zeros(0, np.float32)
+    ts = np.concatenate([r[1] for r in results])
+    x = np.concatenate([r[2] for r in results])
+    o = np.argsort(ts, kind="stable")
+    return ts[o], x[o]
+
+
+def http_fetch(url, timeout=30):
+    with urllib.request.urlopen(url, timeout=timeout) as r:
+        return r.read()
+
+
+def _rows(mats, width):
+    m = np.zeros((len(mats), max(4, A.row_pitch(width))), np.float32)
+    lens = np.zeros(len(mats), np.uint32)
+    for i, x in enumerate(mats):
+        n = min(x.size, width)
+        m[i, :n] = x[-n:] if n else x[:0]     # keep the most recent points when over-long
+        lens[i] = n
+    return m, lens
+
+
+def score_documents(ctx, docs, fetch=http_fetch, type_names=None, max_hist=10080, max_base=None):
+    """Score every metric of every document in ONE coalesced batch.
+
+    docs: dicts with the Document fields (id, currentConfig, baselineConfig,
+    historicalConfig, strategy).  Returns {id: {"status", "reason", "anomalyInfo",
+    "processingContent", "metrics"}}.  A document whose configs cannot be parsed
+    or fetched gets "preprocess_failed" with the reason; scoring the others goes on.
+    """
+    type_names = type_names or dict(A.METRIC_TYPES)
+    series = []       # (doc idx, alias, ts_cur, cur, base, hist)
+    results = {}
+    for di, doc in enumerate(docs):
+        try:
+            cur_cfg = parse_config(doc.get("currentConfig", ""))
+            if not cur_cfg:
+                raise ValueError("currentConfig is empty")
+            strat = (doc.get("strategy") or "").lower()
+            base_cfg = parse_config(doc.get("baselineConfig", "")) if strat in CANARY_STRATEGIES else {}
+            hist_cfg = parse_config(doc.get("historicalConfig", ""))
+            for alias, url in cur_cfg.items():
+                ts, cur = merge_series(decode_query_range(fetch(url)))
+                base = merge_series(decode_query_range(fetch(base_cfg[alias])))[1] if alias in base_cfg else None
+                hist = merge_series(decode_query_range(fetch(hist_cfg[alias])))[1] if alias in hist_cfg else None
+                series.append((di, alias, ts, cur, base, hist))
+        except Exception as e:  # host I/O problem: the document fails, the batch goes on
+            series = [s for s in series if s[0] != di]
+            results[doc["id"]] = {"status": ST_PRE_FAILED, "reason": f"{type(e).__name__}: {e}",
+                                  "anomalyInfo": "", "processingContent": "", "metrics": {}}
+    out = {}
+    # canary series (with a baseline) and historical-only series are two batches
+    for canary in (True, False):
+        idx = [i for i, s in enumerate(series) if (s[4] is not None) == canary]
+        if not idx:
+            continue
+        cur_w = max(1, max(series[i][3].size for i in idx))
+        if cur_w > A.FM_MAX_CUR:
+            cur_w = A.FM_MAX_CUR
+        cur, cl = _rows([series[i][3] for i in idx], cur_w)
+        hist = hl = base = bl = None
+        if any(series[i][5] is not None for i in idx):
+            hw = min(max_hist, max(1, max((series[i][5].size if series[i][5] is not None else 0) for i in idx)))
+            hist, hl = _rows([series[i][5] if series[i][5] is not None else np.zeros(0, np.float32) for i in idx], hw)
+        if canary:
+            bw = max(1, max(series[i][4].size for i in idx))
+            bw = min(bw, max_base or (A.FM_MAX_RANK_N - cur_w))
+            base, bl = _rows([series[i][4] for i in idx], bw)
+        mt = np.array([metric_type_id(series[i][1], type_names) for i in idx], np.uint8)
+        r = ctx.score(cur, base, hist, strategy=A.FM_STRAT_CANARY if canary else A.FM_STRAT_HISTORICAL,
+                      cur_len=cl, base_len=bl, hist_len=hl, metric_type=mt)
+        for j, i in enumerate(idx):
+            out[i] = r["rec"][j]
+    # per document: A.9 roll-up over its metrics, reason, anomalyInfo (models.go:60-63;
+    # values are [t0, v0, t1, v1, ...] as decoded by Barrelman.go:593-620)
+    for di, doc in enumerate(docs):
+        if doc["id"] in results:
+            continue
+        mine = [(i, s) for i, s in enumerate(series) if s[0] == di]
+        verdicts = [int(out[i]["verdict"]) for i, _ in mine]
+        if any(v == A.FM_UNHEALTHY for v in verdicts):
+            verdict = A.FM_UNHEALTHY
+        elif verdicts and all(v == A.FM_UNKNOWN for v in verdicts):
+            verdict = A.FM_UNKNOWN
+        elif not verdicts:
+            verdict = A.FM_UNKNOWN
+        else:
+            verdict = A.FM_HEALTHY
+        anomaly, reasons, metrics = {}, [], {}
+        for i, (_, alias, ts, cur, _b, _h) in mine:
+            rec = out[i]
+            metrics[alias] = {k: (float(rec[k]) if rec[k].dtype.kind == "f" else int(rec[k])) for k in rec.dtype.names}
+            if rec["verdict"] == A.FM_UNHEALTHY:
+                n = min(cur.size, A.FM_MAX_CUR)
+                off = cur.size - n
+                x = cur[off:].astype(np.float64)
+                bm = int(ctx.table[metric_type_id(alias, type_names) if metric_type_id(alias, type_names) < len(ctx.table) else 0].bound_mask)
+                flag = ((bm & 1) != 0) & (x > rec["upper"]) | ((bm & 2) != 0) & (x < rec["lower"])
+                vals = []
+                for k in np.nonzero(flag)[0]:
+                    vals += [int(ts[off + k]), float(x[k])]
+                anomaly[alias] = {"tags": "", "values": vals}
+                reasons.append(f"{alias}: {int(rec['n_anom'])} anomalous point(s) outside "
+                               f"[{rec['lower']:.6g}, {rec['upper']:.6g}]")
+            elif rec["verdict"] == A.FM_UNKNOWN:
+                reasons.append(f"{alias}: " + ("no current metric" if rec["status"] & A.FM_ST_NO_CURRENT
+                                               else "not enough historical data"))
+        results[doc["id"]] = {"status": VERDICT_STATUS[verdict], "reason": "; ".join(reasons),
+                              "anomalyInfo": json.dumps(anomaly) if anomaly else "",
+                              "processingContent": "", "metrics": metrics}
+    return results
+
+
+class MemoryStore:
+    """Stand-in for the Elasticsearch 'documents' index (elasticsearchstore.go:16-19)
+    with the two operations the brain needs: search by status, update."""
+
+    def __init__(self, docs=()):
+        self.docs = {d["id"]: dict(d) for d in docs}
+
+    def by_status(self, statuses, limit=1000):
+        return [dict(d) for d in self.docs.values() if d.get("status") in statuses][:limit]
+
+    def update(self, doc_id, expect_modified_at=None, **fields):
+        d = self.docs[doc_id]
+        if expect_modified_at is not None and d.get("modified_at") != expect_modified_at:
+            return False                                  # somebody else claimed it
+        d.update(fields)
+        return True
+
+
+class BrainWorker:
+    """Poll / claim / score / write-back loop (design.md:37-43).
+
+    - claims "initial" documents by moving them to preprocess_inprogress with a
+      modified_at stamp; a document stuck in an *_inprogress state for longer
+      than MAX_STUCK_IN_SECONDS (foremast-brain.yaml:80-81) is taken over;
+    - fail fast: unhealthy completes the job at once; a healthy verdict before
+      endTime puts the job back to "initial" so it is re-judged on the next poll
+      ("continuous to monitor ... until endTime is reached", design.md:43);
+    - all claimed documents of one poll are scored as one batch.
+    """
+
+    def __init__(self, ctx, store, fetch=http_fetch, env=None, now=time.time):
+        self.ctx, self.store, self.fetch, self.now = ctx, store, fetch, now
+        env = env or {}
+        self.max_stuck = float(env.get("MAX_STUCK_IN_SECONDS", "90"))
+        g, table, names = params_from_env(env)
+        self.type_names = names
+        ctx.set_params(g, table)
+
+    def claim(self):
+        now = self.now()
+        claimed = []
+        for d in self.store.by_status({ST_INITIAL, ST_PRE_INPROGRESS, ST_POST_INPROGRESS}):
+            if d["status"] != ST_INITIAL and now - float(d.get("modified_at", 0)) <= self.max_stuck:
+                continue                                   # another worker is on it
+            if self.store.update(d["id"], expect_modified_at=d.get("modified_at"),
+                                 status=ST_PRE_INPROGRESS, modified_at=now):
+                d["status"], d["modified_at"] = ST_PRE_INPROGRESS, now
+                claimed.append(d)
+        return claimed
+
+    def poll_once(self):
+        docs = self.claim()
+        if not docs:
+            return {}
+        res = score_documents(self.ctx, docs, self.fetch, self.type_names)
+        now = self.now()
+        for d in docs:
+            r = res[d["id"]]
+            status = r["status"]
+            end = d.get("endTime")
+            if status == ST_HEALTH and end is not None and now < float(end):
+                status = ST_INITIAL                       # keep watching until endTime
+            self.store.update(d["id"], status=status, reason=r["reason"], anomalyInfo=r["anomalyInfo"],
+                              modified_at=now)
+            r["written_status"] = status
+        return res

@@ -1,0 +1,179 @@
+"""Host logic of the brain mirror (no GPU): config strings, env knobs, Prometheus
+decoding, status mapping, job loop.  Scoring is delegated to a stand-in context
+that answers with the CPU oracle, so only the host code is under test here; the
+same flow against the real library is tests/test_gpu_brain.py."""
+import ctypes as C
+import json
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from foremast_1_b200 import _abi as A
+from foremast_1_b200 import brain as B
+from foremast_1_b200.engine import _as_matrix
+
+
+class OracleCtx:
+    """engine.Context look-alike backed by the oracle (tests only)."""
+
+    def __init__(self):
+        self.g, self.table = A.default_params()
+
+    def set_params(self, g, table):
+        self.g, self.table = g, table
+
+    def score(self, cur, base=None, hist=None, *, strategy, cur_len=None, base_len=None,
+              hist_len=None, metric_type=None, **kw):
+        cur, nc = _as_matrix(cur)
+        base, nb = _as_matrix(base)
+        hist, nh = _as_matrix(hist)
+        b = A.Batch()
+        b.struct_size = C.sizeof(A.Batch)
+        b.strategy, b.n_series = strategy, cur.shape[0]
+        b.cur, b.n_cur, b.cur_pitch = A.ptr(cur), nc, cur.shape[1]
+        keep = [cur, base, hist, cur_len, base_len, hist_len, metric_type]
+        if base is not None:
+            b.base, b.n_base, b.base_pitch = A.ptr(base), nb, base.shape[1]
+        if hist is not None:
+            b.hist, b.n_hist, b.hist_pitch = A.ptr(hist), nh, hist.shape[1]
+        b.cur_len, b.base_len, b.hist_len = A.ptr(cur_len), A.ptr(base_len), A.ptr(hist_len)
+        b.metric_type = A.ptr(metric_type)
+        out = O.score_batch(self.g, self.table, b, n_threads=2)
+        out["_keep"] = keep
+        return out
+
+
+def prom(ts0, values, step=60, metric=None):
+    return json.dumps({"status": "success", "data": {"resultType": "matrix", "result": [
+        {"metric": metric or {}, "values": [[ts0 + i * step, str(v)] for i, v in enumerate(values)]}]}})
+
+
+def test_config_string_round_trip():
+    d = {"error5xx": "http://prom/api/v1/query_range?query=a%7Bb%3D%22c%22%7D&start=1&end=2&step=60",
+         "latency": "http://prom/api/v1/query_range?query=l&start=1&end=2&step=60"}
+    s = B.format_config(d)
+    assert s.count(B.CONFIG_SEPARATOR) == 1 and "error5xx== http" in s      # main.go:28-31
+    assert B.parse_config(s) == d
+    assert B.parse_config("") == {}
+    with pytest.raises(ValueError):
+        B.parse_config("no separator here")
+
+
+def test_external_status_mapping():
+    # pkg/converter/converter.go:11-30
+    m = {"initial": "new", "preprocess_inprogress": "inprogress", "postprocess_inprogress": "inprogress",
+         "preprocess_completed": "inprogress", "completed_health": "success", "completed_unhealth": "anomaly",
+         "completed_unknown": "abort", "preprocess_failed": "abort", "abort": "abort", "whatever": "inprogress"}
+    for k, v in m.items():
+        assert B.external_status(k) == v
+
+
+# the env block of deploy/foremast/3_brain/foremast-brain.yaml:24-81
+DEPLOYED_ENV = {"ML_ALGORITHM": "moving_average_all", "threshold": "2.0", "min_lower_bound": "0", "bound": "1",
+           "metric_type_threshold_count": "5",
+           "metric_type0": "error5xx", "threshold0": "2", "bound0": "1", "min_lower_bound0": "0",
+           "metric_type1": "error4xx", "threshold1": "3", "bound1": "1", "min_lower_bound1": "0",
+           "metric_type2": "latency", "threshold2": "10", "bound2": "3", "min_lower_bound2": "0",
+           "metric_type3": "cpu", "threshold3": "5", "bound3": "1", "min_lower_bound3": "0",
+           "metric_type4": "memory", "threshold4": "5", "bound4": "1", "min_lower_bound4": "0",
+           "MIN_MANN_WHITE_DATA_POINTS": "20", "MIN_WILCOXON_DATA_POINTS": "20",
+           "MIN_KRUSKAL_DATA_POINTS": "5", "MAX_STUCK_IN_SECONDS": "90"}
+
+
+def test_params_from_deployed_env():
+    g, table, names = B.params_from_env(DEPLOYED_ENV)
+    dg, dt = A.default_params()
+    assert bytes(g) == bytes(dg) and bytes(table) == bytes(dt)
+    assert names == A.METRIC_TYPES
+    assert B.metric_type_id("latency", names) == 3
+    assert B.metric_type_id("namespace_app_per_pod:http_server_requests_error5xx", names) == 1
+    assert B.metric_type_id("something_else", names) == 0
+    with pytest.raises(ValueError):
+        B.params_from_env({"ML_ALGORITHM": "prophet"})
+    with pytest.raises(ValueError):
+        B.params_from_env({"bound": "4"})
+    g2, _, _ = B.params_from_env({"ML_PAIRWISE_ALGORITHM": "mann_white", "ML_PAIRWISE_THRESHOLD": "0.01"})
+    assert g2.pairwise_mode == A.FM_PW_MANN_WHITE and g2.alpha == 0.01
+
+
+def test_decode_query_range_drops_gaps_and_merges_pods():
+    body = json.dumps({"status": "success", "data": {"result": [
+        {"metric": {"pod": "a"}, "values": [[100, "1.5"], [160, "NaN"], [220, "2.5"]]},
+        {"metric": {"pod": "b"}, "values": [[130, "7"], [190, "+Inf"]]}]}})
+    res = B.decode_query_range(body)
+    assert [r[2].tolist() for r in res] == [[1.5, 2.5], [7.0]]
+    ts, x = B.merge_series(res)
+    assert ts.tolist() == [100, 130, 220] and x.tolist() == [1.5, 7.0, 2.5]
+    assert B.decode_query_range(json.dumps(body))[0][2].tolist() == [1.5, 2.5]   # double-encoded proxy reply
+    with pytest.raises(ValueError):
+        B.decode_query_range('{"status":"error","error":"boom"}')
+    assert B.merge_series([])[1].size == 0
+
+
+def make_docs():
+    rng = np.random.default_rng(0)
+    hist = rng.normal(100, 5, 600)
+    store = {
+        "http://p/h_lat": prom(0, hist), "http://p/b_lat": prom(40000, rng.normal(100, 5, 60)),
+        "http://p/c_lat_ok": prom(50000, rng.normal(100, 5, 30)),
+        "http://p/c_lat_bad": prom(50000, np.concatenate([rng.normal(100, 5, 28), [400.0, 420.0]])),
+        "http://p/h_err": prom(0, rng.integers(0, 3, 600) / 60), "http://p/c_err": prom(50000, rng.integers(0, 3, 30) / 60),
+        "http://p/empty": json.dumps({"status": "success", "data": {"result": []}}),
+    }
+    docs = [
+        {"id": "ok", "strategy": "canary", "status": "initial", "modified_at": 0.0,
+         "currentConfig": B.format_config({"latency": "http://p/c_lat_ok", "error5xx": "http://p/c_err"}),
+         "baselineConfig": B.format_config({"latency": "http://p/b_lat"}),
+         "historicalConfig": B.format_config({"latency": "http://p/h_lat", "error5xx": "http://p/h_err"})},
+        {"id": "bad", "strategy": "rollingUpdate", "status": "initial", "modified_at": 0.0,
+         "currentConfig": B.format_config({"latency": "http://p/c_lat_bad"}), "baselineConfig": "",
+         "historicalConfig": B.format_config({"latency": "http://p/h_lat"})},
+        {"id": "nocur", "strategy": "continuous", "status": "initial", "modified_at": 0.0,
+         "currentConfig": B.format_config({"latency": "http://p/empty"}), "baselineConfig": "",
+         "historicalConfig": B.format_config({"latency": "http://p/h_lat"})},
+        {"id": "broken", "strategy": "canary", "status": "initial", "modified_at": 0.0,
+         "currentConfig": B.format_config({"latency": "http://p/404"}), "baselineConfig": "", "historicalConfig": ""},
+    ]
+    return docs, (lambda url: store[url])
+
+
+def check_scored(res):
+    assert res["ok"]["status"] == B.ST_HEALTH and res["ok"]["anomalyInfo"] == ""
+    assert set(res["ok"]["metrics"]) == {"latency", "error5xx"}
+    assert res["bad"]["status"] == B.ST_UNHEALTH
+    info = json.loads(res["bad"]["anomalyInfo"])
+    vals = info["latency"]["values"]          # [t0, v0, t1, v1] (Barrelman.go:593-620)
+    assert vals == [50000 + 28 * 60, 400.0, 50000 + 29 * 60, 420.0]
+    assert "latency: 2 anomalous" in res["bad"]["reason"]
+    assert res["nocur"]["status"] == B.ST_UNKNOWN and "no current metric" in res["nocur"]["reason"]
+    assert res["broken"]["status"] == B.ST_PRE_FAILED and "KeyError" in res["broken"]["reason"]
+
+
+def test_score_documents_statuses_and_anomaly_info():
+    docs, fetch = make_docs()
+    check_scored(B.score_documents(OracleCtx(), docs, fetch))
+
+
+def test_worker_claim_takeover_and_fail_fast():
+    docs, fetch = make_docs()
+    for d in docs:
+        d["endTime"] = 1000.0
+    docs.append(dict(docs[0], id="stuck", status=B.ST_PRE_INPROGRESS, modified_at=5.0))
+    docs.append(dict(docs[0], id="busy", status=B.ST_PRE_INPROGRESS, modified_at=95.0))
+    store = B.MemoryStore(docs)
+    clock = [100.0]
+    w = B.BrainWorker(OracleCtx(), store, fetch, env=DEPLOYED_ENV, now=lambda: clock[0])
+    res = w.poll_once()
+    # "stuck" (95 s old) is taken over, "busy" (5 s old) is left to its owner
+    assert "stuck" in res and "busy" not in res and store.docs["busy"]["status"] == B.ST_PRE_INPROGRESS
+    # fail fast: unhealthy completes now; healthy before endTime goes back to the queue
+    assert store.docs["bad"]["status"] == B.ST_UNHEALTH
+    assert store.docs["ok"]["status"] == B.ST_INITIAL and res["ok"]["status"] == B.ST_HEALTH
+    assert store.docs["nocur"]["status"] == B.ST_UNKNOWN
+    clock[0] = 2000.0
+    res = w.poll_once()
+    assert store.docs["ok"]["status"] == B.ST_HEALTH and B.external_status(store.docs["ok"]["status"]) == "success"
+    assert "bad" not in res                       # completed documents are not re-scored
+    # an optimistic-lock loser does not claim
+    assert store.update("ok", expect_modified_at=-1.0, status="x") is False

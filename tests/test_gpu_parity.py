@@ -187,7 +187,8 @@ def test_rollup(ctx):
                        metric_type=mt, api_id=api, api_service=svc, n_apis=S // 4, n_services=S // 32)
     assert out["svc"]["severity"][0] == A.FM_UNKNOWN
     assert (out["svc"]["n_children"] == 8).all()
-    assert set(np.unique(out["svc"]["severity"])) >= {A.FM_HEALTHY, A.FM_UNHEALTHY}
+    assert (out["svc"]["severity"][1:] != A.FM_UNKNOWN).all()
+    assert set(np.unique(out["api"]["severity"])) == {A.FM_HEALTHY, A.FM_UNHEALTHY, A.FM_UNKNOWN}
 
 
 def test_multi_chunk_pipeline(ctx):
