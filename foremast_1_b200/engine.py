@@ -111,6 +111,7 @@ class Context:
         b.cur_len, b.base_len, b.hist_len = A.ptr(cl), A.ptr(bl), A.ptr(hl)
         mt = None if metric_type is None else np.ascontiguousarray(metric_type, dtype=np.uint8)
         b.metric_type = A.ptr(mt)
+        keep.append(mt)
         ai, asv = u32(api_id), u32(api_service)
         b.api_id, b.api_service = A.ptr(ai), A.ptr(asv)
         b.n_apis, b.n_services = int(n_apis), int(n_services)
