@@ -32,6 +32,7 @@ SYMBOLS = {
     "fm_score_groups_device": (C.c_int32, [C.c_void_p, C.POINTER(A.GroupBatch), C.c_void_p, C.c_void_p, C.POINTER(A.Timing)]),
     "fm_rank_dump": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p]),
     "fm_ma_window_series": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "fm_ma_window_series_static": (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
     "fm_synth_fill_device": (C.c_int32, [C.c_void_p, C.POINTER(A.SynthDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fm_synth_fill_host": (C.c_int32, [C.POINTER(A.SynthDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "fm_ctx_sync": (C.c_int32, [C.c_void_p]),

@@ -61,6 +61,16 @@ int32_t fail(fm_ctx* c, int32_t code, const char* fmt, ...) {
   return code;
 }
 
+}  // namespace
+
+void fm_set_thread_error(const char* fmt, ...) {
+  char buf[512];
+  va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+  g_create_error = buf;
+}
+
+namespace {
+
 #define FM_CK(ctx, call)                                                              \
   do {                                                                                \
     cudaError_t e__ = (call);                                                         \

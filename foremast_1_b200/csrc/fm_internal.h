@@ -65,5 +65,8 @@ int fm_launch_ma_window(const float* d_x, uint32_t n, uint32_t w, uint32_t ddof,
 int fm_launch_synth(const fm_synth_desc& d, float* cur, float* base, float* hist, uint8_t* mt,
                     cudaStream_t st);
 
+// message for fm_last_error(NULL) of the calling thread (entry points that take no ctx)
+void fm_set_thread_error(const char* fmt, ...);
+
 cudaError_t fm_score_smem_attr(int bytes);
 cudaError_t fm_groups_smem_attr(int bytes);

@@ -13,6 +13,7 @@
 //   a5..a8  fp64 p-values, pairwise decision, thresholds, anomaly ballot.
 //   a9  roll-up counters by atomics into the per-API output records.
 #include <cstdint>
+#include <mutex>
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
@@ -476,6 +477,72 @@ int fm_launch_ma_window(const float* d_x, uint32_t n, uint32_t w, uint32_t ddof,
                         double* d_p2, double* d_mean, double* d_sigma, cudaStream_t st) {
   k_ma_window<<<1, 1024, 0, st>>>(d_x, n, w, ddof, d_p1, d_p2, d_mean, d_sigma);
   return 1;
+}
+
+// ---------------------------------------------------------------------------
+// fm_ma_window_series_static: k_ma_window for callers that may not allocate
+// (see include/foremast_cuda.h).  The two prefix-sum arrays that the ctx-based
+// entry point takes from a cudaMalloc'ed arena live here, in a fixed array that
+// is part of the library image on every device.
+//
+// g_ma_static below is a HOST-side handle in host code, not a device address:
+// the kernel must be given the address cudaGetSymbolAddress returns for the
+// device that is current, so that lookup is done once per device and cached.
+static __device__ __align__(256) double g_ma_static[2 * FM_STATIC_MA_MAX_POINTS];
+
+namespace {
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_ma_static_mu;
+double* g_ma_static_addr[kMaxStaticDevices] = {};
+}  // namespace
+
+extern "C" int32_t fm_ma_window_series_static(int32_t device, void* stream, const float* d_x,
+                                              uint32_t n, uint32_t w, uint32_t ddof,
+                                              double* d_mean_out, double* d_sigma_out) {
+  if (device < 0 || device >= kMaxStaticDevices) {
+    fm_set_thread_error("fm_ma_window_series_static: device %d out of range", device);
+    return FM_E_INVALID;
+  }
+  if (n == 0) return FM_OK;
+  if (!d_x || !d_mean_out || !d_sigma_out) {
+    fm_set_thread_error("fm_ma_window_series_static: null device pointer");
+    return FM_E_INVALID;
+  }
+  if (n > FM_STATIC_MA_MAX_POINTS) {
+    fm_set_thread_error("fm_ma_window_series_static: n = %u exceeds the built-in scratch of %u points; "
+                        "use fm_ma_window_series (which allocates) for longer rows",
+                        n, FM_STATIC_MA_MAX_POINTS);
+    return FM_E_UNSUPPORTED;
+  }
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) {
+    fm_set_thread_error("fm_ma_window_series_static: cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    return FM_E_CUDA;
+  }
+  double* scratch;
+  {
+    // set-up, once per device, with that device current
+    std::lock_guard<std::mutex> lk(g_ma_static_mu);
+    if (!g_ma_static_addr[device]) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_ma_static);
+      if (e != cudaSuccess || !p) {
+        fm_set_thread_error("fm_ma_window_series_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        return FM_E_CUDA;
+      }
+      g_ma_static_addr[device] = static_cast<double*>(p);
+    }
+    scratch = g_ma_static_addr[device];
+  }
+  // entries [0, n) of both halves are rewritten by the kernel before it reads them
+  k_ma_window<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(
+      d_x, n, w, ddof, scratch, scratch + FM_STATIC_MA_MAX_POINTS, d_mean_out, d_sigma_out);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    fm_set_thread_error("fm_ma_window_series_static: launch: %s", cudaGetErrorString(e));
+    return FM_E_CUDA;
+  }
+  return FM_OK;
 }
 
 int fm_launch_synth(const fm_synth_desc& d, float* cur, float* base, float* hist, uint8_t* mt,

@@ -308,6 +308,36 @@ int32_t fm_rank_dump(fm_ctx* ctx, const float* cur, uint32_t n_cur,
 int32_t fm_ma_window_series(fm_ctx* ctx, const float* x, uint32_t n, uint32_t w,
                             uint32_t ddof, double* mean_out, double* sigma_out);
 
+/* The same trailing-window series for callers that must not allocate.
+ * (No counterpart in the reference: it exists for hosts of this library.)
+ *
+ * fm_ma_window_series above stages its row and keeps two prefix-sum arrays in
+ * device memory that the ctx obtains with cudaMalloc.  Some embedders cannot
+ * afford that: a service that hands the whole GPU to one pool owner at start-up
+ * and forbids driver allocations afterwards, or a polling loop with a latency
+ * budget that cudaMalloc's device-wide synchronisation would break.  This entry
+ * point needs no ctx and performs no allocation of any kind: the caller passes
+ * DEVICE pointers for the row and both outputs, and the prefix sums live in a
+ * fixed array compiled into the library (2 * FM_STATIC_MA_MAX_POINTS doubles =
+ * 256 KiB, resident on every GPU that loads the library until the process exits).
+ *
+ *   - n > FM_STATIC_MA_MAX_POINTS is refused with FM_E_UNSUPPORTED (message via
+ *     fm_last_error(NULL)); nothing is launched.
+ *   - makes `device` current and queues one kernel on `stream` (a cudaStream_t
+ *     passed as void*, NULL = the default stream); it does not wait for it.
+ *   - the first call on each device looks up the device address of the built-in
+ *     array (once per device); make that first call before starting any stream
+ *     capture on that device.
+ *   - every call on a device shares the one array.  It keeps the previous call's
+ *     prefix sums; that is harmless because each call rewrites entries [0, n)
+ *     before reading them and reads nothing else, so nothing has to be cleared.
+ *     Two calls that overlap on the same GPU (different streams or threads)
+ *     race on it: serialise them. */
+#define FM_STATIC_MA_MAX_POINTS 16384u
+int32_t fm_ma_window_series_static(int32_t device, void* stream, const float* d_x, uint32_t n,
+                                   uint32_t w, uint32_t ddof, double* d_mean_out,
+                                   double* d_sigma_out);
+
 /* Synthetic rows, bit-identical on host and device (include/fm_synth.h).
  * The *_device variant writes device matrices, the *_host variant host ones. */
 int32_t fm_synth_fill_device(fm_ctx* ctx, const fm_synth_desc* d, float* d_cur,
