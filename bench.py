@@ -170,8 +170,11 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--mode", default="", help="override the workload's pairwise mode (diagnostics only)")
     args = ap.parse_args()
     w = dict(WORKLOADS[args.workload])
+    if args.mode:
+        w["mode"] = args.mode
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))

@@ -48,7 +48,10 @@ struct fm_ctx {
   Arena in[2], out[2], roll, misc;
   cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
   std::vector<cudaEvent_t> kev;    // per-chunk kernel timing events
-  int score_smem_set = 0, groups_smem_set = 0;
+  int score_smem_set = 0, groups_smem_set = 0, canary_smem_set = 0, sort_smem_set = 0;
+  int force_path = 0;              // FOREMAST_CUDA_PATH: 1 = generic (shared-memory sort) only,
+                                   // 2 = hash-multiset canary kernel, 0 = auto (register sort)
+  int force_stages = 0;            // FOREMAST_CUDA_STAGES=1|2: staging buffers per warp of the fast path
   std::string err;
 };
 
@@ -85,16 +88,95 @@ uint32_t round4(uint32_t n) { return (n + 3u) & ~3u; }
 
 bool mode_has(uint32_t mode, uint32_t t) { return mode == t || mode == FM_PW_ALL || mode == FM_PW_ANY; }
 
-struct Plan { FmKArgs a; int wpc; int grid; };
+// kind: 0 = k_score_series (generic), 1 = k_canary_fast (hash multiset), 2 = k_canary_sort<regs>
+struct Plan { FmKArgs a; int wpc; int grid; bool fast; int kind; int regs; };
+
+void fill_common(fm_ctx* c, const fm_batch* b, bool canary, FmKArgs& a) {
+  a.cur = b->cur; a.cur_len = b->cur_len; a.n_cur = b->n_cur; a.cur_pitch = b->cur_pitch;
+  a.base = canary ? b->base : nullptr; a.base_len = b->base_len; a.n_base = canary ? b->n_base : 0; a.base_pitch = b->base_pitch;
+  a.hist = b->hist; a.hist_len = b->hist_len; a.n_hist = b->n_hist; a.hist_pitch = b->hist_pitch;
+  a.metric_type = b->metric_type; a.api_id = b->api_id;
+  a.n_series = b->n_series;
+  a.P = c->d_params;
+  a.record_kind = b->record_kind;
+  a.strategy = b->strategy;
+}
+
+// Shared-memory layout and launch shape for k_canary_fast (fm_canary.cu): canary batches with a
+// current row of <= 64 points and a baseline row of <= 1984 points.
+int32_t plan_canary_fast(fm_ctx* c, const fm_batch* b, Plan* pl) {
+  FmKArgs& a = pl->a;
+  a.cur_cap = 64;
+  a.base_cap = round4(b->n_base);
+  a.log_m = 8;
+  while ((1u << a.log_m) < (b->n_cur + b->n_base) * 5u / 2u) ++a.log_m;   // load factor <= 0.4
+  auto bytes = [&](uint32_t stages) {
+    size_t x = 16 + (size_t)stages * (64 + a.base_cap) * 4 + 88 * 4 + ((size_t)4 << a.log_m);
+    return (x + 127) & ~size_t(127);
+  };
+  const size_t limit = c->smem_optin ? c->smem_optin : 232448;
+  const size_t sm_total = 233472 - 1024;
+  a.n_stages = c->force_stages ? (uint32_t)c->force_stages : 2u;
+  a.warp_bytes = (uint32_t)bytes(a.n_stages);
+  int wpc = (int)std::min<size_t>(8, limit / a.warp_bytes);   // k_canary_fast: __launch_bounds__(256)
+  if (wpc < 1) return fail(c, FM_E_UNSUPPORTED, "canary fast path does not fit shared memory");
+  int ctas = (int)std::min<size_t>(8, sm_total / ((size_t)wpc * a.warp_bytes + 1024));
+  if (ctas < 1) ctas = 1;
+  while (ctas * wpc > 64) --ctas;
+  pl->wpc = wpc;
+  const uint64_t need = (b->n_series + wpc - 1) / wpc;
+  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * ctas, need));
+  if (!c->canary_smem_set) { FM_CK(c, fm_canary_smem_attr((int)limit)); c->canary_smem_set = 1; }
+  fill_common(c, b, true, a);
+  pl->fast = true; pl->kind = 1;
+  return FM_OK;
+}
+
+// k_canary_sort<R> (fm_canary_sort.cu): current row <= 64 points, baseline <= 32*R points sorted in
+// registers.  Per warp: mbarrier, one staging buffer (it is re-armed as soon as the rows are in
+// registers) and the parking area of the sorted baseline.
+int32_t plan_canary_sort(fm_ctx* c, const fm_batch* b, Plan* pl) {
+  FmKArgs& a = pl->a;
+  const int R = b->n_base <= 512 ? 16 : (b->n_base <= 1024 ? 32 : 64);
+  a.cur_cap = 64;
+  a.base_cap = round4(b->n_base);
+  a.n_stages = 1;
+  a.warp_bytes = (uint32_t)((16 + (size_t)(64 + a.base_cap) * 4 + (size_t)128 * R + 127) & ~size_t(127));
+  const size_t limit = c->smem_optin ? c->smem_optin : 232448;
+  const size_t sm_total = 233472;
+  // register budget: __launch_bounds__(256, 2) caps the kernel at 128 registers -> 16 warps per SM
+  int best_w = 1, best_total = 0;
+  for (int w = 1; w <= 8; ++w) {
+    const size_t cta = (size_t)w * a.warp_bytes;
+    if (cta > limit) break;
+    int ctas = (int)(sm_total / (cta + 1024));
+    ctas = std::min(ctas, 16 / w);
+    if (ctas < 1) continue;
+    if (ctas * w >= best_total) { best_total = ctas * w; best_w = w; }
+  }
+  if (best_total == 0) return fail(c, FM_E_UNSUPPORTED, "canary sort path does not fit shared memory");
+  pl->wpc = best_w;
+  const uint64_t need = (b->n_series + best_w - 1) / best_w;
+  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * (best_total / best_w), need));
+  if (!c->sort_smem_set) { FM_CK(c, fm_canary_sort_smem_attr((int)limit)); c->sort_smem_set = 1; }
+  fill_common(c, b, true, a);
+  pl->fast = true; pl->kind = 2; pl->regs = R;
+  return FM_OK;
+}
 
 // Shared-memory layout and launch shape for k_score_series.
 int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
   FmKArgs& a = pl->a;
   memset(&a, 0, sizeof(a));
+  pl->fast = false; pl->kind = 0; pl->regs = 0;
   const bool canary = b->strategy == FM_STRAT_CANARY && b->base != nullptr;
   if (b->n_cur > FM_MAX_CUR) return fail(c, FM_E_UNSUPPORTED, "n_cur %u > %u", b->n_cur, FM_MAX_CUR);
   if (canary && (uint64_t)b->n_cur + b->n_base > FM_MAX_RANK_N)
     return fail(c, FM_E_UNSUPPORTED, "n_cur + n_base %u > %u", b->n_cur + b->n_base, FM_MAX_RANK_N);
+  if (canary && c->force_path != 1 && b->n_cur <= 64 && b->n_base >= 1) {
+    if (c->force_path == 2 && b->n_base <= 1984) return plan_canary_fast(c, b, pl);
+    if (b->n_base <= 2048) return plan_canary_sort(c, b, pl);
+  }
   a.cur_cap = std::max(4u, round4(b->n_cur));
   a.cs_cap = pow2_ceil(b->n_cur, 64u);
   a.base_cap = canary ? pow2_ceil(b->n_base, 64u) : 0u;
@@ -139,6 +221,12 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
   a.record_kind = b->record_kind;
   a.strategy = b->strategy;
   return FM_OK;
+}
+
+int launch_plan(const Plan& pl, cudaStream_t st) {
+  if (pl.kind == 2) return fm_launch_canary_sort(pl.a, pl.regs, pl.wpc, pl.grid, st);
+  if (pl.kind == 1) return fm_launch_canary_fast(pl.a, pl.wpc, pl.grid, st);
+  return fm_launch_score(pl.a, pl.wpc, pl.grid, st);
 }
 
 int32_t validate_batch(fm_ctx* c, const fm_batch* b, const void* out) {
@@ -238,6 +326,9 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
     { fail(nullptr, FM_E_UNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); delete c; return FM_E_UNSUPPORTED; }
   c->num_sms = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
+  if (const char* e = getenv("FOREMAST_CUDA_PATH"))
+    c->force_path = strcmp(e, "generic") == 0 ? 1 : (strcmp(e, "hash") == 0 ? 2 : 0);
+  if (const char* e = getenv("FOREMAST_CUDA_STAGES")) c->force_stages = (e[0] == '1') ? 1 : (e[0] == '2' ? 2 : 0);
   FM_CKC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   FM_CKC(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
   FM_CKC(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
@@ -366,7 +457,7 @@ int32_t fm_score_batch_device(fm_ctx* c, const fm_batch* b, void* d_out, fm_rank
     if (d_svc && b->api_service) FM_CK(c, cudaMemsetAsync(d_svc, 0, (size_t)b->n_services * sizeof(fm_rollup_rec), c->stream));
   }
   if (timing) FM_CK(c, cudaEventRecord(c->ev_a, c->stream));
-  launches += fm_launch_score(pl.a, pl.wpc, pl.grid, c->stream);
+  launches += launch_plan(pl, c->stream);
   if (timing) FM_CK(c, cudaEventRecord(c->ev_m, c->stream));
   if (roll)
     launches += fm_launch_rollup_finalize(d_api, b->n_apis, b->api_service,
@@ -481,7 +572,7 @@ int32_t fm_score_batch(fm_ctx* c, const fm_batch* b, void* out, fm_rank_aux* out
     FM_CK(c, cudaStreamWaitEvent(c->stream, c->in_ready[s], 0));
     if (ci >= 2) FM_CK(c, cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
     FM_CK(c, cudaEventRecord(c->kev[2 * ci], c->stream));
-    launches += fm_launch_score(pl.a, pl.wpc, pl.grid, c->stream);
+    launches += launch_plan(pl, c->stream);
     FM_CK(c, cudaGetLastError());
     FM_CK(c, cudaEventRecord(c->kev[2 * ci + 1], c->stream));
     FM_CK(c, cudaEventRecord(c->in_free[s], c->stream));

@@ -1,0 +1,545 @@
+// fm_canary_sort.cu — canary hot path, register-resident ranking (BASELINE.json configs[0..2]).
+//
+// One warp per series, persistent over the batch:
+//   a1  the row pair (current <= 64 points, baseline <= 32*R points) arrives in the warp's shared
+//       memory stage through the TMA unit (cp.async.bulk + mbarrier); as soon as the warp has
+//       pulled the rows into registers (conflict-free 128-bit LDS) it re-arms the same stage for
+//       its NEXT series, so the copy runs under the whole ranking of the current one.
+//   a2  pivoted fp64 moments from the registers, warp-shuffle reduction.
+//   a4  the baseline row is sorted IN REGISTERS by a bitonic network over the warp: R keys per
+//       lane (blocked), strides < R are lane-local FMNMX pairs, strides >= R one SHFL.BFLY + one
+//       predicated FMNMX per key.  Tie term from the run lengths (lane-local scan + a 5-step
+//       segmented warp scan for runs that cross lanes).  The sorted row is then parked in shared
+//       memory (transposed, conflict-free) and each current point finds its lower / upper bound
+//       there: 2*R1 = n1(n1+1) + sum(2*lb + (ub - lb)).
+//       Wilcoxon: 64 fp64 |differences| sorted across the warp, tie runs by warp scans.
+//   a5..a9  one erfc for the three p-values (lanes 0..2), decision, thresholds, anomaly ballot,
+//       fused roll-up atomics.
+// All the work is regular (no data-dependent loops), so the cost per series does not depend on
+// how many ties the data has.  Integers (rank sums, tie terms) are bit-identical to the
+// sort-in-shared-memory path of fm_kernels.cu and to the oracle.
+#include <cstdint>
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include "fm_device.cuh"
+
+namespace {
+
+constexpr uint32_t kCur = 64;
+constexpr unsigned long long kAbsMask = 0x7FFFFFFFFFFFFFFFull;
+
+__device__ __forceinline__ uint32_t row_len(const uint32_t* len, uint64_t s, uint32_t n) {
+  return len ? min(__ldg(len + s), n) : n;
+}
+
+__device__ __forceinline__ void issue_rows(const FmKArgs& a, float* stage, uint64_t* bar, uint64_t s,
+                                           uint32_t nc, uint32_t nb) {
+  const uint32_t cb = ((nc + 3u) & ~3u) * 4u, bb = ((nb + 3u) & ~3u) * 4u;
+  fm_mbar_expect_tx(bar, cb + bb);
+  if (cb) fm_bulk_g2s(stage, a.cur + s * a.cur_pitch, cb, bar);
+  if (bb) fm_bulk_g2s(stage + kCur, a.base + s * a.base_pitch, bb, bar);
+}
+
+// ---- 64 keys across the warp (a = index lane, b = index lane + 32) -------------------------
+__device__ __forceinline__ void sort64(float& a, float& b, int lane) {
+#pragma unroll
+  for (int k = 2; k <= 64; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j == 32) {
+        const float lo = fminf(a, b), hi = fmaxf(a, b);
+        a = lo; b = hi;
+      } else {
+        const bool up_a = (lane & k) == 0, up_b = ((lane + 32) & k) == 0;
+        const bool lower = (lane & j) == 0;
+        const float oa = __shfl_xor_sync(FM_FULL, a, j), ob = __shfl_xor_sync(FM_FULL, b, j);
+        a = (lower == up_a) ? fminf(a, oa) : fmaxf(a, oa);
+        b = (lower == up_b) ? fminf(b, ob) : fmaxf(b, ob);
+      }
+    }
+  }
+}
+__device__ __forceinline__ void cex64(unsigned long long& v, unsigned long long o, bool take_min) {
+  const unsigned long long vm = v & kAbsMask, om = o & kAbsMask;
+  const bool repl = take_min ? (om < vm) : (vm < om);
+  v = repl ? o : v;
+}
+__device__ __forceinline__ void sort64_abs(unsigned long long& a, unsigned long long& b, int lane) {
+#pragma unroll
+  for (int k = 2; k <= 64; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j == 32) {
+        const unsigned long long a0 = a, b0 = b;
+        cex64(a, b0, true);
+        cex64(b, a0, false);
+      } else {
+        const bool up_a = (lane & k) == 0, up_b = ((lane + 32) & k) == 0;
+        const bool lower = (lane & j) == 0;
+        const unsigned long long oa = __shfl_xor_sync(FM_FULL, a, j), ob = __shfl_xor_sync(FM_FULL, b, j);
+        cex64(a, oa, lower == up_a);
+        cex64(b, ob, lower == up_b);
+      }
+    }
+  }
+}
+
+// For a sorted 64-key sequence (positions lane and lane + 32; `sa`/`sb` = my key differs from the
+// previous position's): start of my tie run (lo) and the first run start after me (e, exclusive end).
+__device__ __forceinline__ void runs64(bool sa, bool sb, int lane, uint32_t& lo_a, uint32_t& lo_b,
+                                       uint32_t& e_a, uint32_t& e_b) {
+  lo_a = sa ? (uint32_t)lane : 0u; lo_b = sb ? (uint32_t)lane + 32u : 0u;
+  uint32_t hi_a = sa ? (uint32_t)lane : 64u, hi_b = sb ? (uint32_t)lane + 32u : 64u;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t ua = __shfl_up_sync(FM_FULL, lo_a, o), ub = __shfl_up_sync(FM_FULL, lo_b, o);
+    const uint32_t da = __shfl_down_sync(FM_FULL, hi_a, o), db = __shfl_down_sync(FM_FULL, hi_b, o);
+    if (lane >= o) { lo_a = max(lo_a, ua); lo_b = max(lo_b, ub); }
+    if (lane + o < 32) { hi_a = min(hi_a, da); hi_b = min(hi_b, db); }
+  }
+  lo_b = max(lo_b, __shfl_sync(FM_FULL, lo_a, 31));
+  const uint32_t first_b = __shfl_sync(FM_FULL, hi_b, 0);
+  hi_a = min(hi_a, first_b);
+  e_a = __shfl_down_sync(FM_FULL, hi_a, 1);
+  e_b = __shfl_down_sync(FM_FULL, hi_b, 1);
+  if (lane == 31) { e_a = first_b; e_b = 64u; }
+}
+
+// ---- 32*R keys, R per lane, blocked: key index = R*lane + r --------------------------------
+// Bitonic sort in its all-ascending form: phase K first compares i with i ^ (K-1) ("flip"), then
+// i with i ^ J for J = K/4 .. 1; the lower index always keeps the minimum, so every lane-local
+// stage is a fixed pair of FMNMX on fixed registers (no per-lane direction to select on).
+// Template recursion over (K, J) keeps every register index a compile-time constant (a rolled
+// loop would push v[] to local memory).
+template <int R, int K>
+__device__ __forceinline__ void sort_flip(float (&v)[R], int lane) {
+  if constexpr (K > R) {
+    // partner: lane ^ (K/R - 1), register R-1-r.  Pairs (r, R-1-r) are exchanged together so that
+    // both shuffles read values from before this stage.
+    const bool take_min = ((lane * R) & (K / 2)) == 0;
+#pragma unroll
+    for (int r = 0; r < R / 2; ++r) {
+      const float o1 = __shfl_xor_sync(FM_FULL, v[R - 1 - r], K / R - 1);
+      const float o2 = __shfl_xor_sync(FM_FULL, v[r], K / R - 1);
+      v[r] = take_min ? fminf(v[r], o1) : fmaxf(v[r], o1);
+      v[R - 1 - r] = take_min ? fminf(v[R - 1 - r], o2) : fmaxf(v[R - 1 - r], o2);
+    }
+  } else {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if ((r & (K / 2)) == 0) {
+        const float x = v[r], y = v[r ^ (K - 1)];
+        v[r] = fminf(x, y);
+        v[r ^ (K - 1)] = fmaxf(x, y);
+      }
+    }
+  }
+}
+template <int R, int J>
+__device__ __forceinline__ void sort_disperse(float (&v)[R], int lane) {
+  if constexpr (J >= R) {
+    const bool take_min = ((lane * R) & J) == 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float o = __shfl_xor_sync(FM_FULL, v[r], J / R);
+      v[r] = take_min ? fminf(v[r], o) : fmaxf(v[r], o);
+    }
+  } else {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if ((r & J) == 0) {
+        const float x = v[r], y = v[r | J];
+        v[r] = fminf(x, y);
+        v[r | J] = fmaxf(x, y);
+      }
+    }
+  }
+}
+template <int R, int J>
+struct SortMerge {
+  static __device__ __forceinline__ void run(float (&v)[R], int lane) {
+    sort_disperse<R, J>(v, lane);
+    SortMerge<R, J / 2>::run(v, lane);
+  }
+};
+template <int R>
+struct SortMerge<R, 0> {
+  static __device__ __forceinline__ void run(float (&)[R], int) {}
+};
+template <int R, int K, bool Done>
+struct SortPhase {
+  static __device__ __forceinline__ void run(float (&v)[R], int lane) {
+    sort_flip<R, K>(v, lane);
+    SortMerge<R, K / 4>::run(v, lane);
+    SortPhase<R, K * 2, (K * 2 > 32 * R)>::run(v, lane);
+  }
+};
+template <int R, int K>
+struct SortPhase<R, K, true> {
+  static __device__ __forceinline__ void run(float (&)[R], int) {}
+};
+template <int R>
+__device__ __forceinline__ void sort_rows(float (&v)[R], int lane) {
+  SortPhase<R, 2, false>::run(v, lane);
+}
+
+// transposed parking of the sorted row: key index i = R*lane + r lives at word r*32 + lane
+template <int R>
+__device__ __forceinline__ uint32_t park_addr(uint32_t base_s, uint32_t i) {
+  return base_s + (((i & (R - 1)) << 5) + (i / R)) * 4u;
+}
+template <int R>
+__device__ __forceinline__ uint32_t parked_lower(uint32_t base_s, uint32_t n, float x) {
+  uint32_t lo = 0, len = n;
+  while (len) {
+    const uint32_t h = len >> 1;
+    if (fm_lds_f32(park_addr<R>(base_s, lo + h)) < x) { lo += h + 1; len -= h + 1; } else len = h;
+  }
+  return lo;
+}
+template <int R>
+__device__ __forceinline__ uint32_t parked_upper(uint32_t base_s, uint32_t n, float x) {
+  uint32_t lo = 0, len = n;
+  while (len) {
+    const uint32_t h = len >> 1;
+    if (!(x < fm_lds_f32(park_addr<R>(base_s, lo + h)))) { lo += h + 1; len -= h + 1; } else len = h;
+  }
+  return lo;
+}
+
+struct Prep { bool run; bool degenerate; double stat; double arg; };   // p = min(1, erfc(arg))
+
+template <int R>
+__global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int wpc = blockDim.x >> 5;
+  unsigned char* wp = smem + (size_t)warp * a.warp_bytes;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(wp);
+  float* stage = reinterpret_cast<float*>(wp + 16);
+  const uint32_t stage_s = fm_smem_u32(stage), base_s = stage_s + kCur * 4u;
+  const uint32_t park_s = stage_s + (kCur + a.base_cap) * 4u;
+  const fm_global_params& g = a.P->g;
+
+  if (lane == 0) { fm_mbar_init(bar, 1); fm_fence_mbar_init(); }
+  __syncwarp();
+
+  const uint64_t stride = (uint64_t)gridDim.x * wpc;
+  uint64_t s = (uint64_t)blockIdx.x * wpc + warp;
+  uint32_t phase = 0;
+  if (s < a.n_series && lane == 0)
+    issue_rows(a, stage, bar, s, row_len(a.cur_len, s, a.n_cur), row_len(a.base_len, s, a.n_base));
+
+  for (; s < a.n_series; s += stride) {
+    const uint32_t nc = row_len(a.cur_len, s, a.n_cur);
+    const uint32_t nb = row_len(a.base_len, s, a.n_base);
+    const uint64_t sn = s + stride;
+    fm_mbar_wait(bar, phase);
+    phase ^= 1u;
+
+    const uint32_t ty = a.metric_type ? a.metric_type[s] : 0u;
+    const fm_type_params tp = a.P->types[ty < a.P->n_types ? ty : 0u];
+    fm_series_rec rec;
+    fm_rec_init(rec);
+    fm_rank_aux ax = {0, 0, 0, 0, 0, 0u, 0u};
+    uint32_t status = 0;
+    if (nc == 0) status |= FM_ST_NO_CURRENT;
+
+    const bool pair = g.pairwise_mode != FM_PW_NONE && nc > 0 && nb > 0;
+    const bool want_mw = pair && fm_mode_has(g.pairwise_mode, FM_PW_MANN_WHITE) && nc >= g.min_mw && nb >= g.min_mw;
+    const bool want_kw = pair && fm_mode_has(g.pairwise_mode, FM_PW_KRUSKAL) && nc >= g.min_kw && nb >= g.min_kw;
+    const bool want_wx = pair && fm_mode_has(g.pairwise_mode, FM_PW_WILCOXON);
+    const bool ranks = want_mw || want_kw;
+    const bool fuse_model = (a.hist == nullptr) && g.ma_mode == FM_MA_ALL;
+
+    // ---- rows into registers (everything that needs time order is read here) --------------
+    const float craw_a = (uint32_t)lane < nc ? fm_lds_f32(stage_s + 4u * lane) : 0.0f;
+    const float craw_b = (uint32_t)lane + 32u < nc ? fm_lds_f32(stage_s + 4u * (lane + 32u)) : 0.0f;
+    const float ca = (uint32_t)lane < nc ? craw_a + 0.0f : CUDART_INF_F;
+    const float cb = (uint32_t)lane + 32u < nc ? craw_b + 0.0f : CUDART_INF_F;
+
+    // Wilcoxon differences (pairs need the baseline in time order)
+    unsigned long long ka = kAbsMask, kb = kAbsMask;
+    uint32_t nz = 0, n_pairs = 0;
+    if (want_wx) {
+      n_pairs = min(nc, nb);
+      const uint32_t oc = g.pair_rule == FM_PAIR_TAIL ? nc - n_pairs : 0u;
+      const uint32_t ob = g.pair_rule == FM_PAIR_TAIL ? nb - n_pairs : 0u;
+      if ((uint32_t)lane < n_pairs) {
+        const double d = __dsub_rn((double)fm_lds_f32(stage_s + 4u * (oc + lane)),
+                                   (double)fm_lds_f32(base_s + 4u * (ob + lane)));
+        if (d != 0.0) ka = (unsigned long long)__double_as_longlong(d); else ++nz;
+      }
+      if ((uint32_t)lane + 32u < n_pairs) {
+        const double d = __dsub_rn((double)fm_lds_f32(stage_s + 4u * (oc + lane + 32u)),
+                                   (double)fm_lds_f32(base_s + 4u * (ob + lane + 32u)));
+        if (d != 0.0) kb = (unsigned long long)__double_as_longlong(d); else ++nz;
+      }
+    }
+
+    // baseline: vector c of lane = float4 #(lane + 32 c); any assignment of points to lanes will do
+    // for a sort, this one is bank-conflict free.  Missing points are +inf and sort to the end.
+    float v[R];
+    const double pivot = nb ? (double)fm_lds_f32(base_s) : 0.0;
+    FmMom mom = {0.0, 0.0};
+    if (ranks || fuse_model) {
+#pragma unroll
+      for (int c = 0; c < R / 4; ++c) {
+        const uint32_t e0 = ((uint32_t)lane + 32u * c) << 2;
+        float4 q = make_float4(CUDART_INF_F, CUDART_INF_F, CUDART_INF_F, CUDART_INF_F);
+        if (e0 < nb) q = fm_lds_v4(base_s + (e0 << 2));
+        const bool full = 128u * c + 127u < nb;          // warp-uniform: the whole vector row is valid
+        if (!full) {
+          if (e0 + 1u >= nb) q.y = CUDART_INF_F;
+          if (e0 + 2u >= nb) q.z = CUDART_INF_F;
+          if (e0 + 3u >= nb) q.w = CUDART_INF_F;
+        }
+        v[4 * c + 0] = q.x + 0.0f; v[4 * c + 1] = q.y + 0.0f;
+        v[4 * c + 2] = q.z + 0.0f; v[4 * c + 3] = q.w + 0.0f;
+        if (fuse_model) {
+          if (full) {
+            fm_mom_add(mom, q.x, pivot); fm_mom_add(mom, q.y, pivot);
+            fm_mom_add(mom, q.z, pivot); fm_mom_add(mom, q.w, pivot);
+          } else {
+            if (e0 < nb) fm_mom_add(mom, q.x, pivot);
+            if (e0 + 1u < nb) fm_mom_add(mom, q.y, pivot);
+            if (e0 + 2u < nb) fm_mom_add(mom, q.z, pivot);
+            if (e0 + 3u < nb) fm_mom_add(mom, q.w, pivot);
+          }
+        }
+      }
+    }
+
+    // ---- a2: model ---------------------------------------------------------------------------
+    bool model_ok;
+    if (a.hist) {
+      model_ok = fm_model(g, a.hist + s * a.hist_pitch, row_len(a.hist_len, s, a.n_hist), true, lane,
+                          rec.mean, rec.sigma);
+    } else if (fuse_model) {
+      model_ok = nb >= max(g.min_hist_points, g.ddof + 1u);
+      if (model_ok) fm_moments_finish(mom, pivot, nb, g.ddof, rec.mean, rec.sigma);
+    } else {
+      model_ok = fm_model(g, stage + kCur, nb, false, lane, rec.mean, rec.sigma);
+    }
+    if (!model_ok) status |= FM_ST_HIST_INSUFFICIENT;
+
+    // the stage has been consumed: let the TMA unit fill it with this warp's next series
+    __syncwarp();
+    if (sn < a.n_series) {
+      fm_fence_proxy_async();
+      if (lane == 0)
+        issue_rows(a, stage, bar, sn, row_len(a.cur_len, sn, a.n_cur), row_len(a.base_len, sn, a.n_base));
+    }
+
+    // ---- Wilcoxon signed rank (A.4) -----------------------------------------------------------
+    Prep t_wx = {false, false, 0.0, 0.0};
+    if (want_wx) {
+      nz = fm_warp_sum(nz);
+      const uint32_t np = n_pairs - nz;
+      ax.n_wx = np;
+      if (np >= g.min_wx && np > 0) {
+        sort64_abs(ka, kb, lane);
+        const unsigned long long ma = ka & kAbsMask, mb = kb & kAbsMask;
+        const unsigned long long pa = __shfl_up_sync(FM_FULL, ma, 1);
+        const unsigned long long last_a = __shfl_sync(FM_FULL, ma, 31);
+        unsigned long long pb = __shfl_up_sync(FM_FULL, mb, 1);
+        if (lane == 0) pb = last_a;
+        uint32_t lo_a, lo_b, e_a, e_b;
+        runs64(lane == 0 || pa != ma, pb != mb, lane, lo_a, lo_b, e_a, e_b);
+        long long wp = 0, wm = 0, T = 0;
+        if ((uint32_t)lane < np) {
+          const long long r2 = (long long)(lo_a + e_a + 1u), t = (long long)(e_a - lo_a);
+          if (ka >> 63) wm += r2; else wp += r2;
+          T += t * t - 1;
+        }
+        if ((uint32_t)lane + 32u < np) {
+          const long long r2 = (long long)(lo_b + e_b + 1u), t = (long long)(e_b - lo_b);
+          if (kb >> 63) wm += r2; else wp += r2;
+          T += t * t - 1;
+        }
+        wp = fm_warp_sum(wp); wm = fm_warp_sum(wm); T = fm_warp_sum(T);
+        ax.w2_plus = wp; ax.w2_minus = wm; ax.t_wx = T;
+        t_wx.run = true;
+        const double wmin = 0.5 * (double)(wp < wm ? wp : wm);
+        const double dn = (double)np;
+        const double mu = dn * (dn + 1.0) / 4.0;
+        const double var = dn * (dn + 1.0) * (2.0 * dn + 1.0) / 24.0 - (double)T / 48.0;
+        t_wx.stat = wmin;
+        if (!(var > 0.0)) t_wx.degenerate = true;
+        else {
+          double num = wmin - mu;
+          if (g.cc_wx && num != 0.0) num += 0.5;
+          t_wx.arg = fabs(num / sqrt(var)) / 1.4142135623730951;
+        }
+      }
+    }
+
+    // ---- Mann-Whitney / Kruskal: sort the baseline in registers -------------------------------
+    Prep t_mw = {false, false, 0.0, 0.0}, t_kw = {false, false, 0.0, 0.0};
+    if (ranks) {
+      sort_rows<R>(v, lane);
+
+      // tie runs of the sorted baseline; position i = R*lane + r counts while i < nb
+      const uint32_t i0 = (uint32_t)lane * R;
+      const uint32_t nvalid = nb > i0 ? min(nb - i0, (uint32_t)R) : 0u;
+      uint32_t run = 1, acc = 0;                  // acc = sum of c(c+1), c = run position
+#pragma unroll
+      for (int r = 1; r < R; ++r) {
+        const bool eq = (v[r] == v[r - 1]) && ((uint32_t)r < nvalid);
+        run = eq ? run + 1u : 1u;
+        acc += eq ? (run - 1u) * run : 0u;
+      }
+      unsigned long long T = 3ull * acc;
+      // runs that continue from the previous lane: c_in = points of my first value before me
+      float vlast = v[0];
+#pragma unroll
+      for (int r = 1; r < R; ++r) vlast = ((uint32_t)r < nvalid) ? v[r] : vlast;
+      const float prev_last = __shfl_up_sync(FM_FULL, vlast, 1);
+      const uint32_t prev_tail = __shfl_up_sync(FM_FULL, run, 1);      // prev lane: run at its last key
+      const bool prev_full = __shfl_up_sync(FM_FULL, (run == (uint32_t)R) ? 1 : 0, 1) != 0;
+      const bool link = lane > 0 && nvalid > 0 && prev_last == v[0];
+      uint32_t cin = link ? prev_tail : 0u;
+      bool cont = link && prev_full;               // previous lane is one single run: add its carry too
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t cu = __shfl_up_sync(FM_FULL, cin, o);
+        const int bu = __shfl_up_sync(FM_FULL, cont ? 1 : 0, o);
+        if (lane >= o && cont) { cin += cu; cont = bu != 0; }
+      }
+      // park the sorted row (transposed: conflict-free) and look up my head run and the current points
+#pragma unroll
+      for (int r = 0; r < R; ++r) fm_sts_f32(park_s + ((uint32_t)(r * 32 + lane) << 2), v[r]);
+      __syncwarp();
+      if (cin > 0) {
+        // my head run; what lies beyond this lane is corrected by the lanes that hold it
+        const uint32_t hlen = min(parked_upper<R>(park_s, nb, v[0]) - i0, nvalid);
+        const unsigned long long h = hlen, c = cin;
+        T += h * (3ull * c * (c + h));           // tie_gain(cin, hlen) - tie_gain(0, hlen)
+      }
+
+      // current row: sorted for its own tie positions, each point located in the parked baseline
+      float sa = ca, sb = cb;
+      sort64(sa, sb, lane);
+      const float qa = __shfl_up_sync(FM_FULL, sa, 1);
+      const float last_sa = __shfl_sync(FM_FULL, sa, 31);
+      float qb = __shfl_up_sync(FM_FULL, sb, 1);
+      if (lane == 0) qb = last_sa;
+      uint32_t lo_a, lo_b, e_a, e_b;
+      runs64(lane == 0 || qa != sa, qb != sb, lane, lo_a, lo_b, e_a, e_b);
+      long long r2c = 0;
+      if ((uint32_t)lane < nc) {
+        const uint32_t lb = parked_lower<R>(park_s, nb, sa), tb = parked_upper<R>(park_s, nb, sa) - lb;
+        const unsigned long long c = tb + ((uint32_t)lane - lo_a);
+        r2c += 2ll * lb + tb;
+        T += 3ull * c * (c + 1ull);
+      }
+      if ((uint32_t)lane + 32u < nc) {
+        const uint32_t lb = parked_lower<R>(park_s, nb, sb), tb = parked_upper<R>(park_s, nb, sb) - lb;
+        const unsigned long long c = tb + ((uint32_t)lane + 32u - lo_b);
+        r2c += 2ll * lb + tb;
+        T += 3ull * c * (c + 1ull);
+      }
+      r2c = fm_warp_sum(r2c) + (long long)nc * (nc + 1);
+      const long long Tt = fm_warp_sum((long long)T);
+      ax.r2_cur = r2c; ax.t_mw = Tt;
+      const double N = (double)nc + (double)nb;
+      if (want_mw) {
+        t_mw.run = true;
+        const double u1 = 0.5 * (double)(r2c - (long long)nc * ((long long)nc + 1));
+        const double u2 = (double)nc * (double)nb - u1;
+        const double u = u1 > u2 ? u1 : u2;
+        const double mu = 0.5 * (double)nc * (double)nb;
+        const double var = ((double)nc * (double)nb / 12.0) * ((N + 1.0) - (double)Tt / (N * (N - 1.0)));
+        t_mw.stat = u1;
+        if (!(var > 0.0)) t_mw.degenerate = true;
+        else t_mw.arg = ((u - mu - (g.cc_mw ? 0.5 : 0.0)) / sqrt(var)) / 1.4142135623730951;
+      }
+      if (want_kw) {
+        t_kw.run = true;
+        const double rx = 0.5 * (double)r2c;
+        const double ry = 0.5 * (double)((long long)(nc + nb) * ((long long)(nc + nb) + 1) - r2c);
+        const double sres = rx * rx / (double)nc + ry * ry / (double)nb;
+        const double h0 = 12.0 / (N * (N + 1.0)) * sres - 3.0 * (N + 1.0);
+        const double c = 1.0 - (double)Tt / (N * N * N - N);
+        if (!(c > 0.0)) t_kw.degenerate = true;
+        else {
+          t_kw.stat = h0 / c;
+          t_kw.arg = t_kw.stat > 0.0 ? sqrt(0.5 * t_kw.stat) : -1.0;   // chi2 sf, 1 dof; H <= 0 -> 1
+        }
+      }
+    }
+
+    // ---- a5: one erfc for the three tests (lanes 0, 1, 2) -------------------------------------
+    const double arg = lane == 0 ? t_mw.arg : (lane == 1 ? t_wx.arg : t_kw.arg);
+    double pe = erfc(arg);
+    pe = pe > 1.0 ? 1.0 : pe;
+    const double p_mw = __shfl_sync(FM_FULL, pe, 0), p_wx = __shfl_sync(FM_FULL, pe, 1),
+                 p_kw = __shfl_sync(FM_FULL, pe, 2);
+    const double pv_mw = t_mw.degenerate ? 1.0 : p_mw, pv_wx = t_wx.degenerate ? 1.0 : p_wx,
+                 pv_kw = t_kw.degenerate ? 1.0 : p_kw;
+    if (t_mw.run) { rec.u1 = t_mw.stat; rec.p_u = pv_mw; status |= FM_ST_MW_RUN; }
+    if (t_wx.run) { rec.w = t_wx.stat; rec.p_w = pv_wx; status |= FM_ST_WX_RUN; }
+    if (t_kw.run) { rec.h = t_kw.degenerate ? 0.0 : t_kw.stat; rec.p_h = pv_kw; status |= FM_ST_KW_RUN; }
+    if ((t_mw.run && t_mw.degenerate) || (t_wx.run && t_wx.degenerate) || (t_kw.run && t_kw.degenerate))
+      status |= FM_ST_DEGENERATE;
+
+    // ---- a6..a8 --------------------------------------------------------------------------------
+    bool differ = false;
+    if (pair) {
+      const bool e0 = t_mw.run && !t_mw.degenerate, e1 = t_wx.run && !t_wx.degenerate,
+                 e2 = t_kw.run && !t_kw.degenerate;
+      const bool d0 = pv_mw < g.alpha, d1 = pv_wx < g.alpha, d2 = pv_kw < g.alpha;
+      const bool any = (e0 && d0) || (e1 && d1) || (e2 && d2);
+      const bool all = (!e0 || d0) && (!e1 || d1) && (!e2 || d2);
+      if (!(e0 || e1 || e2)) status |= FM_ST_PAIRWISE_SKIPPED;
+      else differ = g.pairwise_mode == FM_PW_ALL ? all : any;
+      if (differ) status |= FM_ST_DIFFER;
+    }
+    if (model_ok && nc > 0) {
+      // A.7 / A.8 on the current points held in registers (time order: lane, lane + 32)
+      const double k = differ ? tp.k_low : tp.k;
+      const double up = __dadd_rn(rec.mean, __dmul_rn(k, rec.sigma));
+      double lo = __dsub_rn(rec.mean, __dmul_rn(k, rec.sigma));
+      if (lo < tp.min_lower_bound) lo = tp.min_lower_bound;
+      rec.upper = up; rec.lower = lo;
+      const double xa = (double)craw_a, xb = (double)craw_b;
+      const bool fa = (uint32_t)lane < nc && (((tp.bound_mask & 1u) && xa > up) || ((tp.bound_mask & 2u) && xa < lo));
+      const bool fb = (uint32_t)lane + 32u < nc && (((tp.bound_mask & 1u) && xb > up) || ((tp.bound_mask & 2u) && xb < lo));
+      const uint32_t ba = __ballot_sync(FM_FULL, fa), bb = __ballot_sync(FM_FULL, fb);
+      const uint64_t mask = (uint64_t)ba | ((uint64_t)bb << 32);
+      const uint32_t cnt = (uint32_t)__popc(ba) + (uint32_t)__popc(bb);
+      rec.n_anom = cnt;
+      rec.first_idx = (uint16_t)(mask ? (uint32_t)__ffsll((long long)mask) - 1u : 0xFFFFu);
+      rec.anom_mask = mask;
+      rec.verdict = (cnt >= g.min_anomaly_points && cnt > 0) ? FM_UNHEALTHY : FM_HEALTHY;
+    }
+    if (status & (FM_ST_NO_CURRENT | FM_ST_HIST_INSUFFICIENT)) rec.verdict = FM_UNKNOWN;
+    rec.status = (uint8_t)status;
+
+    if (lane == 0) {
+      fm_write_record(a.out, s, a.record_kind, rec);
+      if (a.aux) a.aux[s] = ax;
+      if (a.api && a.api_id) fm_rollup_add(a.api, a.api_id[s], rec.verdict);
+    }
+    __syncwarp();
+  }
+}
+
+}  // namespace
+
+cudaError_t fm_canary_sort_smem_attr(int bytes) {
+  cudaError_t e = cudaFuncSetAttribute(k_canary_sort<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_canary_sort<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_canary_sort<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  return e;
+}
+
+int fm_launch_canary_sort(const FmKArgs& a, int regs, int warps_per_cta, int grid, cudaStream_t st) {
+  const size_t smem = (size_t)warps_per_cta * a.warp_bytes;
+  if (regs == 16) k_canary_sort<16><<<grid, warps_per_cta * 32, smem, st>>>(a);
+  else if (regs == 32) k_canary_sort<32><<<grid, warps_per_cta * 32, smem, st>>>(a);
+  else k_canary_sort<64><<<grid, warps_per_cta * 32, smem, st>>>(a);
+  return 1;
+}
