@@ -331,7 +331,9 @@ def main():
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "bytes_per_series": bps, "kernel": "k_score_series",
+                         "bytes_per_series": bps,
+                         "kernel": ("k_canary_sort<%d>" % (16 if w["n_base"] <= 512 else 32 if w["n_base"] <= 1024 else 64))
+                         if (w["canary"] and w["n_cur"] <= 64 and w["n_base"] <= 2048) else "k_score_series",
                          "kernel_ms": main_ms_max / args.steps},
             "verdict_histogram_first_64k": hist_v,
         }

@@ -1,0 +1,190 @@
+// Package cuda binds libforemast_cuda.so (include/foremast_cuda.h) for foremast-service.
+//
+// It is pure marshalling: every number is computed by the library.  The job loop
+// (package brain, one directory up in a real integration) maps verdicts to the
+// document statuses of pkg/converter/converter.go:11-30 and writes reason / anomalyInfo.
+//
+// NOT COMPILED IN THIS REPOSITORY'S CI: the build image has no Go toolchain.  The
+// Python mirror foremast_1_b200/_ffi.py binds the same symbols and is what the tests run.
+//
+// Build: CGO_ENABLED=1 (foremast-service/Dockerfile:12 sets 0 today), -lforemast_cuda on the
+// linker path, include/foremast_cuda.h on the include path.
+package cuda
+
+/*
+#cgo LDFLAGS: -lforemast_cuda
+#include <stdlib.h>
+#include "foremast_cuda.h"
+*/
+import "C"
+
+import (
+	"fmt"
+	"runtime"
+	"unsafe"
+)
+
+// Verdicts (FM_HEALTHY / FM_UNHEALTHY / FM_UNKNOWN).
+const (
+	Healthy   = 0
+	Unhealthy = 1
+	Unknown   = 2
+)
+
+// Strategies.
+const (
+	StrategyCanary     = C.FM_STRAT_CANARY     // canary: current + baseline (+ historical)
+	StrategyHistorical = C.FM_STRAT_HISTORICAL // rollingUpdate / continuous / hpa
+)
+
+// SeriesRec mirrors fm_series_rec (96 bytes).
+type SeriesRec struct {
+	Mean, Sigma, Upper, Lower float64
+	U1, PU, W, PW, H, PH      float64
+	NAnom                     uint32
+	FirstIdx                  uint16
+	Verdict, Status           uint8
+	AnomMask                  uint64
+}
+
+// Ctx is one GPU + one stream; calls on a Ctx must come from one goroutine at a time.
+type Ctx struct{ h *C.fm_ctx }
+
+func init() {
+	if C.fm_sizeof(4) != C.uint32_t(unsafe.Sizeof(SeriesRec{})) {
+		panic("cuda: SeriesRec does not match fm_series_rec")
+	}
+}
+
+func lastError(h *C.fm_ctx) string { return C.GoString(C.fm_last_error(h)) }
+
+// NewCtx binds device `device`.  There is no CPU fallback: it fails without a GPU.
+func NewCtx(device int) (*Ctx, error) {
+	var h *C.fm_ctx
+	if rc := C.fm_ctx_create(C.int32_t(device), &h); rc != C.FM_OK {
+		return nil, fmt.Errorf("fm_ctx_create(%d): %d: %s", device, int(rc), lastError(nil))
+	}
+	c := &Ctx{h}
+	runtime.SetFinalizer(c, func(c *Ctx) { c.Close() })
+	return c, nil
+}
+
+func (c *Ctx) Close() {
+	if c.h != nil {
+		C.fm_ctx_destroy(c.h)
+		c.h = nil
+	}
+}
+
+// TypeParams is one row of the threshold table (threshold{i} / bound{i} / min_lower_bound{i}
+// of deploy/foremast/3_brain/foremast-brain.yaml:26-73).
+type TypeParams struct {
+	K, KLow, MinLowerBound float64
+	BoundMask              uint32
+}
+
+// SetParams installs the env-derived parameters; g is filled by DefaultParams and edited by the caller.
+func (c *Ctx) SetParams(g *C.fm_global_params, table []TypeParams) error {
+	ct := make([]C.fm_type_params, len(table))
+	for i, t := range table {
+		ct[i] = C.fm_type_params{k: C.double(t.K), k_low: C.double(t.KLow),
+			min_lower_bound: C.double(t.MinLowerBound), bound_mask: C.uint32_t(t.BoundMask)}
+	}
+	if rc := C.fm_set_params(c.h, g, &ct[0], C.uint32_t(len(ct))); rc != C.FM_OK {
+		return fmt.Errorf("fm_set_params: %d: %s", int(rc), lastError(c.h))
+	}
+	return nil
+}
+
+// DefaultParams returns the deployed defaults (foremast-brain.yaml:24-79).
+func DefaultParams() (C.fm_global_params, []TypeParams) {
+	var g C.fm_global_params
+	ct := make([]C.fm_type_params, 8)
+	n := C.uint32_t(len(ct))
+	C.fm_default_params(&g, &ct[0], &n)
+	out := make([]TypeParams, int(n))
+	for i := range out {
+		out[i] = TypeParams{float64(ct[i].k), float64(ct[i].k_low), float64(ct[i].min_lower_bound), uint32(ct[i].bound_mask)}
+	}
+	return g, out
+}
+
+// Pinned is a pinned host buffer from fm_alloc_pinned, viewed as []float32.
+type Pinned struct {
+	p unsafe.Pointer
+	F []float32
+}
+
+func AllocPinned(nFloats int) (*Pinned, error) {
+	var p unsafe.Pointer
+	if rc := C.fm_alloc_pinned(C.size_t(nFloats*4), &p); rc != C.FM_OK {
+		return nil, fmt.Errorf("fm_alloc_pinned: %d", int(rc))
+	}
+	return &Pinned{p, unsafe.Slice((*float32)(p), nFloats)}, nil
+}
+
+func (b *Pinned) Free() { C.fm_free_pinned(b.p); b.p = nil; b.F = nil }
+
+// RowPitch is the row pitch in elements for rows of n points (rows start 16-byte aligned).
+func RowPitch(n int) int { return (n + 3) &^ 3 }
+
+// Batch describes S series: series-major matrices in pinned memory, optional ragged lengths.
+type Batch struct {
+	Strategy            uint32
+	N                   int
+	Cur, Base, Hist     *Pinned // Base / Hist may be nil
+	NCur, NBase, NHist  int
+	CurLen, BaseLen, HistLen []uint32 // optional
+	MetricType          []uint8  // optional, index into the threshold table
+}
+
+// Score judges the batch (docs/guides/design.md:35,43) and fills out[0:N].
+func (c *Ctx) Score(b *Batch, out []SeriesRec) error {
+	if len(out) < b.N {
+		return fmt.Errorf("cuda: out has %d records, need %d", len(out), b.N)
+	}
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	u32 := func(s []uint32) *C.uint32_t {
+		if len(s) == 0 {
+			return nil
+		}
+		pin.Pin(&s[0])
+		return (*C.uint32_t)(unsafe.Pointer(&s[0]))
+	}
+	cb := C.fm_batch{struct_size: C.uint32_t(unsafe.Sizeof(C.fm_batch{})), strategy: C.uint32_t(b.Strategy),
+		n_series: C.uint64_t(b.N), record_kind: C.FM_REC_FULL}
+	cb.cur, cb.n_cur, cb.cur_pitch, cb.cur_len = (*C.float)(b.Cur.p), C.uint32_t(b.NCur), C.uint32_t(RowPitch(b.NCur)), u32(b.CurLen)
+	if b.Base != nil {
+		cb.base, cb.n_base, cb.base_pitch, cb.base_len = (*C.float)(b.Base.p), C.uint32_t(b.NBase), C.uint32_t(RowPitch(b.NBase)), u32(b.BaseLen)
+	}
+	if b.Hist != nil {
+		cb.hist, cb.n_hist, cb.hist_pitch, cb.hist_len = (*C.float)(b.Hist.p), C.uint32_t(b.NHist), C.uint32_t(RowPitch(b.NHist)), u32(b.HistLen)
+	}
+	if len(b.MetricType) > 0 {
+		pin.Pin(&b.MetricType[0])
+		cb.metric_type = (*C.uint8_t)(unsafe.Pointer(&b.MetricType[0]))
+	}
+	pin.Pin(&out[0])
+	if rc := C.fm_score_batch(c.h, &cb, unsafe.Pointer(&out[0]), nil, nil, nil, nil); rc != C.FM_OK {
+		return fmt.Errorf("fm_score_batch: %d: %s", int(rc), lastError(c.h))
+	}
+	return nil
+}
+
+// StatusOf maps a roll-up of verdicts to the document status (converter.go:17-22).
+func StatusOf(verdicts []uint8) string {
+	unknown := len(verdicts) > 0
+	for _, v := range verdicts {
+		if v == Unhealthy {
+			return "completed_unhealth"
+		}
+		if v != Unknown {
+			unknown = false
+		}
+	}
+	if unknown {
+		return "completed_unknown"
+	}
+	return "completed_health"
+}
