@@ -48,9 +48,9 @@ struct fm_ctx {
   Arena in[2], out[2], roll, misc;
   cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
   std::vector<cudaEvent_t> kev;    // per-chunk kernel timing events
-  int score_smem_set = 0, groups_smem_set = 0, canary_smem_set = 0, sort_smem_set = 0;
-  int force_path = 0;              // FOREMAST_CUDA_PATH: 1 = generic (shared-memory sort) only,
-                                   // 2 = hash-multiset canary kernel, 0 = auto (register sort)
+  int score_smem_set = 0, groups_smem_set = 0, sort_smem_set = 0, elect_smem_set = 0;
+  int force_path = 0;              // FOREMAST_CUDA_PATH: generic = 1 (shared-memory sort kernel only),
+                                   // elect = 3 (election-multiset canary kernel), else 0 = auto
   int force_stages = 0;            // FOREMAST_CUDA_STAGES=1|2: staging buffers per warp of the fast path
   std::string err;
 };
@@ -88,7 +88,7 @@ uint32_t round4(uint32_t n) { return (n + 3u) & ~3u; }
 
 bool mode_has(uint32_t mode, uint32_t t) { return mode == t || mode == FM_PW_ALL || mode == FM_PW_ANY; }
 
-// kind: 0 = k_score_series (generic), 1 = k_canary_fast (hash multiset), 2 = k_canary_sort<regs>
+// kind: 0 = k_score_series (generic), 2 = k_canary_sort<regs>, 3 = k_canary_elect<regs>
 struct Plan { FmKArgs a; int wpc; int grid; bool fast; int kind; int regs; };
 
 void fill_common(fm_ctx* c, const fm_batch* b, bool canary, FmKArgs& a) {
@@ -102,33 +102,36 @@ void fill_common(fm_ctx* c, const fm_batch* b, bool canary, FmKArgs& a) {
   a.strategy = b->strategy;
 }
 
-// Shared-memory layout and launch shape for k_canary_fast (fm_canary.cu): canary batches with a
-// current row of <= 64 points and a baseline row of <= 1984 points.
-int32_t plan_canary_fast(fm_ctx* c, const fm_batch* b, Plan* pl) {
+// k_canary_elect<NV> (fm_canary_elect.cu): current row <= 64 points, baseline <= 2048 points, one CTA
+// of 128 threads per series.  Per CTA: two mbarriers, one or two staging buffers, the search tree,
+// the current-point slots, two hand-off records, the per-thread overflow lists and the election
+// table (load factor <= 0.4).  a.warp_bytes carries the bytes per CTA.
+int32_t plan_canary_elect(fm_ctx* c, const fm_batch* b, Plan* pl) {
   FmKArgs& a = pl->a;
   a.cur_cap = 64;
   a.base_cap = round4(b->n_base);
   a.log_m = 8;
-  while ((1u << a.log_m) < (b->n_cur + b->n_base) * 5u / 2u) ++a.log_m;   // load factor <= 0.4
+  while ((1u << a.log_m) < (b->n_cur + b->n_base) * 5u / 2u) ++a.log_m;
+  if (getenv("FOREMAST_CUDA_SMALL_TABLE") && a.log_m > 8) --a.log_m;   // experiment: load factor <= 0.8
+  const int nv = std::max(1, (int)((((b->n_base + 3u) >> 2) + 127u) / 128u));
   auto bytes = [&](uint32_t stages) {
-    size_t x = 16 + (size_t)stages * (64 + a.base_cap) * 4 + 88 * 4 + ((size_t)4 << a.log_m);
+    size_t x = fm_canary_elect_fixed_bytes() + (size_t)stages * (64 + a.base_cap) * 4 +
+               (size_t)(4 * nv + 2) * 128 * 2 + ((size_t)4 << a.log_m);
     return (x + 127) & ~size_t(127);
   };
   const size_t limit = c->smem_optin ? c->smem_optin : 232448;
-  const size_t sm_total = 233472 - 1024;
+  const size_t sm_total = 233472;
   a.n_stages = c->force_stages ? (uint32_t)c->force_stages : 2u;
   a.warp_bytes = (uint32_t)bytes(a.n_stages);
-  int wpc = (int)std::min<size_t>(8, limit / a.warp_bytes);   // k_canary_fast: __launch_bounds__(256)
-  if (wpc < 1) return fail(c, FM_E_UNSUPPORTED, "canary fast path does not fit shared memory");
-  int ctas = (int)std::min<size_t>(8, sm_total / ((size_t)wpc * a.warp_bytes + 1024));
+  // the kernel also has 512 B of static shared memory: the dynamic maximum is the opt-in limit minus that
+  if (a.warp_bytes > limit - 1024) return fail(c, FM_E_UNSUPPORTED, "canary election path does not fit shared memory");
+  int ctas = (int)std::min<size_t>(16, sm_total / ((size_t)a.warp_bytes + 1024 + 512));
   if (ctas < 1) ctas = 1;
-  while (ctas * wpc > 64) --ctas;
-  pl->wpc = wpc;
-  const uint64_t need = (b->n_series + wpc - 1) / wpc;
-  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * ctas, need));
-  if (!c->canary_smem_set) { FM_CK(c, fm_canary_smem_attr((int)limit)); c->canary_smem_set = 1; }
+  pl->wpc = 4;
+  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * ctas, b->n_series));
+  if (!c->elect_smem_set) { FM_CK(c, fm_canary_elect_smem_attr((int)limit - 1024)); c->elect_smem_set = 1; }
   fill_common(c, b, true, a);
-  pl->fast = true; pl->kind = 1;
+  pl->fast = true; pl->kind = 3; pl->regs = nv;
   return FM_OK;
 }
 
@@ -175,7 +178,7 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
   if (canary && (uint64_t)b->n_cur + b->n_base > FM_MAX_RANK_N)
     return fail(c, FM_E_UNSUPPORTED, "n_cur + n_base %u > %u", b->n_cur + b->n_base, FM_MAX_RANK_N);
   if (canary && c->force_path != 1 && b->n_cur <= 64 && b->n_base >= 1) {
-    if (c->force_path == 2 && b->n_base <= 1984) return plan_canary_fast(c, b, pl);
+    if (c->force_path == 3 && b->n_base <= 2048) return plan_canary_elect(c, b, pl);
     if (b->n_base <= 2048) return plan_canary_sort(c, b, pl);
   }
   a.cur_cap = std::max(4u, round4(b->n_cur));
@@ -225,8 +228,8 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
 }
 
 int launch_plan(const Plan& pl, cudaStream_t st) {
+  if (pl.kind == 3) return fm_launch_canary_elect(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 2) return fm_launch_canary_sort(pl.a, pl.regs, pl.wpc, pl.grid, st);
-  if (pl.kind == 1) return fm_launch_canary_fast(pl.a, pl.wpc, pl.grid, st);
   return fm_launch_score(pl.a, pl.wpc, pl.grid, st);
 }
 
@@ -328,7 +331,7 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
   c->num_sms = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
   if (const char* e = getenv("FOREMAST_CUDA_PATH"))
-    c->force_path = strcmp(e, "generic") == 0 ? 1 : (strcmp(e, "hash") == 0 ? 2 : 0);
+    c->force_path = strcmp(e, "generic") == 0 ? 1 : (strcmp(e, "elect") == 0 ? 3 : 0);
   if (const char* e = getenv("FOREMAST_CUDA_STAGES")) c->force_stages = (e[0] == '1') ? 1 : (e[0] == '2' ? 2 : 0);
   FM_CKC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   FM_CKC(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));

@@ -89,6 +89,24 @@ __device__ __forceinline__ uint32_t fm_atoms_add(uint32_t a, uint32_t val) {
   return old;
 }
 
+__device__ __forceinline__ void fm_reds_add(uint32_t a, uint32_t val) {   // no return: fire and forget
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(val) : "memory");
+}
+__device__ __forceinline__ uint32_t fm_lds_u16(uint32_t a) {
+  uint16_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fm_sts_u16(uint32_t a, uint32_t v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((uint16_t)v) : "memory");
+}
+// -1 when a < b else 0 (one FSET; three of them add up with one IADD3)
+__device__ __forceinline__ int fm_set_lt(float a, float b) {
+  int r;
+  asm("set.lt.s32.f32 %0, %1, %2;" : "=r"(r) : "f"(a), "f"(b));
+  return r;
+}
+
 __device__ __forceinline__ float4 fm_ldg_stream(const float4* p) {
   float4 r;
   asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"

@@ -35,7 +35,7 @@ struct FmKArgs {
   uint32_t wx_n;           // doubles, raw differences (max pairs)
   uint32_t n_stages;       // 1 or 2 staging buffers per warp
   uint32_t warp_bytes;     // bytes of shared memory per warp
-  uint32_t log_m;          // k_canary_fast: log2 of the multiset table size
+  uint32_t log_m;          // k_canary_elect: log2 of the election table size
 };
 
 struct FmGArgs {
@@ -55,10 +55,11 @@ struct FmGArgs {
 // launchers (fm_kernels.cu); each returns the number of kernels launched
 int fm_launch_score(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st);
 int fm_launch_groups(const FmGArgs& a, int warps_per_cta, int grid, cudaStream_t st);
-int fm_launch_canary_fast(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st);
-cudaError_t fm_canary_smem_attr(int bytes);
 int fm_launch_canary_sort(const FmKArgs& a, int regs, int warps_per_cta, int grid, cudaStream_t st);
 cudaError_t fm_canary_sort_smem_attr(int bytes);
+int fm_launch_canary_elect(const FmKArgs& a, int nv, int grid, cudaStream_t st);
+size_t fm_canary_elect_fixed_bytes();
+cudaError_t fm_canary_elect_smem_attr(int bytes);
 int fm_launch_rollup_finalize(fm_rollup_rec* api, uint32_t n_apis, const uint32_t* api_service,
                               fm_rollup_rec* svc, uint32_t n_services, cudaStream_t st);
 int fm_launch_rollup_finalize_one(fm_rollup_rec* recs, uint64_t n, cudaStream_t st);

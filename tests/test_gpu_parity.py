@@ -16,11 +16,11 @@ from parity import assert_records_match, bound_masks
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module", params=["auto", "generic", "hash", "hash-1stage"])
+@pytest.fixture(scope="module", params=["auto", "generic", "elect", "elect-1stage"])
 def ctx(request):
-    """auto: the register-sort canary kernel (fm_canary_sort.cu) wherever it applies; hash: the
-    hash-multiset canary kernel (fm_canary.cu); generic: the shared-memory sort kernel for
-    everything (FOREMAST_CUDA_PATH is read when the ctx is created)."""
+    """auto: the register-sort canary kernel (fm_canary_sort.cu) wherever it applies; elect: the
+    election-multiset canary kernel (fm_canary_elect.cu); generic: the shared-memory sort kernel
+    for everything (FOREMAST_CUDA_PATH is read when the ctx is created)."""
     import os
     os.environ["FOREMAST_CUDA_PATH"] = request.param.split("-")[0]
     os.environ["FOREMAST_CUDA_STAGES"] = "1" if request.param.endswith("1stage") else "0"
