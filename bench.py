@@ -171,10 +171,15 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--mode", default="", help="override the workload's pairwise mode (diagnostics only)")
+    ap.add_argument("--n-hist", type=int, default=-1, help="override the history length (config 5 sweep)")
+    ap.add_argument("--compact", action="store_true", help="16-byte records (config 5 sweep)")
     args = ap.parse_args()
     w = dict(WORKLOADS[args.workload])
     if args.mode:
         w["mode"] = args.mode
+    if args.n_hist >= 0:
+        w["n_hist"] = args.n_hist
+        w["desc"] += f" [n_hist={args.n_hist}]"
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -220,7 +225,8 @@ def main():
     d_base = ctx.dev_alloc(S * d.base_pitch * 4) if w["n_base"] else None
     d_hist = ctx.dev_alloc(S * d.hist_pitch * 4) if w["n_hist"] else None
     d_mt = ctx.dev_alloc(S)
-    d_out = ctx.dev_alloc(S * A.SERIES_REC.itemsize)
+    rec_dtype = A.COMPACT_REC if args.compact else A.SERIES_REC
+    d_out = ctx.dev_alloc(S * rec_dtype.itemsize)
     ctx.synth_device(d, d_cur, d_base, d_hist, d_mt)
     ctx.sync()
 
@@ -234,7 +240,7 @@ def main():
     if d_hist:
         b.hist, b.n_hist, b.hist_pitch = d_hist, w["n_hist"], d.hist_pitch
     b.metric_type = d_mt
-    b.record_kind = A.FM_REC_FULL
+    b.record_kind = A.FM_REC_COMPACT if args.compact else A.FM_REC_FULL
 
     t = A.Timing()
     for _ in range(args.warmup):
@@ -257,7 +263,7 @@ def main():
     value = world * S * args.steps / (dev_ms_max / 1e3)
 
     # sanity: verdict histogram of the last step (also proves the kernel wrote results)
-    rec = np.zeros(min(S, 65536), A.SERIES_REC)
+    rec = np.zeros(min(S, 65536), rec_dtype)
     ctx.d2h(rec, d_out)
     hist_v = np.bincount(rec["verdict"], minlength=3).tolist()
 
@@ -277,7 +283,7 @@ def main():
         p_base = Pinned((Se, de.base_pitch), np.float32) if w["n_base"] else None
         p_hist = Pinned((Se, de.hist_pitch), np.float32) if w["n_hist"] else None
         p_mt = Pinned((Se,), np.uint8)
-        p_out = Pinned((Se,), A.SERIES_REC)
+        p_out = Pinned((Se,), rec_dtype)
         from foremast_1_b200 import _ffi
         rc = _ffi.lib().fm_synth_fill_host(C.byref(de), p_cur.ptr, p_base.ptr if p_base else None,
                                            p_hist.ptr if p_hist else None, p_mt.ptr, 0)
@@ -292,7 +298,7 @@ def main():
         if p_hist:
             hb.hist, hb.n_hist, hb.hist_pitch = p_hist.ptr, w["n_hist"], de.hist_pitch
         hb.metric_type = p_mt.ptr
-        hb.record_kind = A.FM_REC_FULL
+        hb.record_kind = b.record_kind
         te = A.Timing()
         ctx.score_host(hb, p_out.ptr, timing=te)   # warm-up (arena growth, first touch)
         barrier()
@@ -314,7 +320,7 @@ def main():
 
     if rank == 0:
         peak, peak_src = measured_peak()
-        rec_bytes = A.SERIES_REC.itemsize
+        rec_bytes = rec_dtype.itemsize
         bps = algorithmic_bytes(w, rec_bytes)
         achieved = S * bps / (main_ms_max / args.steps / 1e3) / 1e9
         line = {
@@ -333,7 +339,8 @@ def main():
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "bytes_per_series": bps,
                          "kernel": ("k_canary_sort<%d>" % (16 if w["n_base"] <= 512 else 32 if w["n_base"] <= 1024 else 64))
-                         if (w["canary"] and w["n_cur"] <= 64 and w["n_base"] <= 2048) else "k_score_series",
+                         if (w["canary"] and w["n_cur"] <= 64 and w["n_base"] <= 2048) else
+                         ("k_ma_only<%d>" % (32 if w["n_hist"] >= 512 else 16 if w["n_hist"] >= 160 else 8)),
                          "kernel_ms": main_ms_max / args.steps},
             "verdict_histogram_first_64k": hist_v,
         }

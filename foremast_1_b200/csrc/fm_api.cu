@@ -88,7 +88,7 @@ uint32_t round4(uint32_t n) { return (n + 3u) & ~3u; }
 
 bool mode_has(uint32_t mode, uint32_t t) { return mode == t || mode == FM_PW_ALL || mode == FM_PW_ANY; }
 
-// kind: 0 = k_score_series (generic), 2 = k_canary_sort<regs>, 3 = k_canary_elect<regs>
+// kind: 0 = k_score_series (generic), 2 = k_canary_sort<regs>, 3 = k_canary_elect<regs>, 4 = k_ma_only<regs>
 struct Plan { FmKArgs a; int wpc; int grid; bool fast; int kind; int regs; };
 
 void fill_common(fm_ctx* c, const fm_batch* b, bool canary, FmKArgs& a) {
@@ -168,6 +168,19 @@ int32_t plan_canary_sort(fm_ctx* c, const fm_batch* b, Plan* pl) {
   return FM_OK;
 }
 
+// k_ma_only<G> (fm_ma.cu): no baseline, plain moving_average_all model, current row <= 64 points.
+int32_t plan_ma_only(fm_ctx* c, const fm_batch* b, Plan* pl) {
+  FmKArgs& a = pl->a;
+  fill_common(c, b, false, a);
+  pl->regs = b->n_hist >= 512 ? 32 : (b->n_hist >= 160 ? 16 : 8);      // lanes per series
+  const uint64_t per_warp = 32 / pl->regs;
+  const uint64_t need = (b->n_series + per_warp * 8 - 1) / (per_warp * 8);   // 8 warps per CTA
+  pl->wpc = 8;
+  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * 8, need));
+  pl->fast = true; pl->kind = 4;
+  return FM_OK;
+}
+
 // Shared-memory layout and launch shape for k_score_series.
 int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
   FmKArgs& a = pl->a;
@@ -177,6 +190,8 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
   if (b->n_cur > FM_MAX_CUR) return fail(c, FM_E_UNSUPPORTED, "n_cur %u > %u", b->n_cur, FM_MAX_CUR);
   if (canary && (uint64_t)b->n_cur + b->n_base > FM_MAX_RANK_N)
     return fail(c, FM_E_UNSUPPORTED, "n_cur + n_base %u > %u", b->n_cur + b->n_base, FM_MAX_RANK_N);
+  if (!canary && c->force_path != 1 && b->hist && b->n_cur <= 64 && c->params.g.ma_mode == FM_MA_ALL)
+    return plan_ma_only(c, b, pl);
   if (canary && c->force_path != 1 && b->n_cur <= 64 && b->n_base >= 1) {
     if (c->force_path == 3 && b->n_base <= 2048) return plan_canary_elect(c, b, pl);
     if (b->n_base <= 2048) return plan_canary_sort(c, b, pl);
@@ -228,6 +243,7 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
 }
 
 int launch_plan(const Plan& pl, cudaStream_t st) {
+  if (pl.kind == 4) return fm_launch_ma_only(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 3) return fm_launch_canary_elect(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 2) return fm_launch_canary_sort(pl.a, pl.regs, pl.wpc, pl.grid, st);
   return fm_launch_score(pl.a, pl.wpc, pl.grid, st);

@@ -180,18 +180,30 @@ __device__ __forceinline__ void fm_moments_global(const float* __restrict__ x, u
   FmMom m = {0.0, 0.0};
   const uint32_t n4 = n >> 2;
   const float4* x4 = reinterpret_cast<const float4*>(x);
-  uint32_t i = lane;
-  for (; i + 96 < n4; i += 128) {  // 4 independent 16-byte loads in flight per lane
-    const float4 a = fm_ldg_stream(x4 + i), b = fm_ldg_stream(x4 + i + 32),
-                 c = fm_ldg_stream(x4 + i + 64), d = fm_ldg_stream(x4 + i + 96);
-    fm_mom_add(m, a.x, pivot); fm_mom_add(m, a.y, pivot); fm_mom_add(m, a.z, pivot); fm_mom_add(m, a.w, pivot);
-    fm_mom_add(m, b.x, pivot); fm_mom_add(m, b.y, pivot); fm_mom_add(m, b.z, pivot); fm_mom_add(m, b.w, pivot);
-    fm_mom_add(m, c.x, pivot); fm_mom_add(m, c.y, pivot); fm_mom_add(m, c.z, pivot); fm_mom_add(m, c.w, pivot);
-    fm_mom_add(m, d.x, pivot); fm_mom_add(m, d.y, pivot); fm_mom_add(m, d.z, pivot); fm_mom_add(m, d.w, pivot);
+  // software pipelined: the next four 16-byte loads of a lane are in flight while the current
+  // four are accumulated
+  float4 q[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    q[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (lane + 32u * j < n4) q[j] = fm_ldg_stream(x4 + lane + 32u * j);
   }
-  for (; i < n4; i += 32) {
-    const float4 a = fm_ldg_stream(x4 + i);
-    fm_mom_add(m, a.x, pivot); fm_mom_add(m, a.y, pivot); fm_mom_add(m, a.z, pivot); fm_mom_add(m, a.w, pivot);
+  for (uint32_t i = lane; i < n4; i += 128) {
+    float4 r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      r[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      const uint32_t v = i + 32u * (4 + j);
+      if (v < n4) r[j] = fm_ldg_stream(x4 + v);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (i + 32u * j < n4) {
+        fm_mom_add(m, q[j].x, pivot); fm_mom_add(m, q[j].y, pivot);
+        fm_mom_add(m, q[j].z, pivot); fm_mom_add(m, q[j].w, pivot);
+      }
+      q[j] = r[j];
+    }
   }
   const uint32_t t = (n4 << 2) + lane;
   if (t < n) fm_mom_add(m, __ldg(x + t), pivot);

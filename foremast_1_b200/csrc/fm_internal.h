@@ -59,6 +59,7 @@ int fm_launch_canary_sort(const FmKArgs& a, int regs, int warps_per_cta, int gri
 cudaError_t fm_canary_sort_smem_attr(int bytes);
 int fm_launch_canary_elect(const FmKArgs& a, int nv, int grid, cudaStream_t st);
 size_t fm_canary_elect_fixed_bytes();
+int fm_launch_ma_only(const FmKArgs& a, int group, int grid, cudaStream_t st);
 cudaError_t fm_canary_elect_smem_attr(int bytes);
 int fm_launch_rollup_finalize(fm_rollup_rec* api, uint32_t n_apis, const uint32_t* api_service,
                               fm_rollup_rec* svc, uint32_t n_services, cudaStream_t st);
