@@ -92,6 +92,16 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(kernel, n_series):
+    """DRAM bytes of one launch from the committed ncu capture of that kernel (None if not captured)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01", "traffic.json")) as f:
+            t = json.load(f).get(kernel)
+        return None if t is None else int(t["bytes_per_series"]) * int(n_series)
+    except Exception:
+        return None
+
+
 def params_for(w):
     from foremast_1_b200 import _abi as A
     g, table = A.default_params()
@@ -323,6 +333,10 @@ def main():
         rec_bytes = rec_dtype.itemsize
         bps = algorithmic_bytes(w, rec_bytes)
         achieved = S * bps / (main_ms_max / args.steps / 1e3) / 1e9
+        kernel = (("k_canary_sort<%d>" % (16 if w["n_base"] <= 512 else 32 if w["n_base"] <= 1024 else 64))
+                  if (w["canary"] and w["n_cur"] <= 64 and w["n_base"] <= 2048) else
+                  ("k_ma_only<%d>" % (32 if w["n_hist"] >= 512 else 16 if w["n_hist"] >= 160 else 8)))
+        traffic = measured_traffic(kernel, S) if (args.n_hist < 0 and not args.mode) else None
         line = {
             "metric": "series scored/sec", "value": value, "unit": "series/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms_max / args.steps,
@@ -336,11 +350,9 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "bytes_per_series": bps,
-                         "kernel": ("k_canary_sort<%d>" % (16 if w["n_base"] <= 512 else 32 if w["n_base"] <= 1024 else 64))
-                         if (w["canary"] and w["n_cur"] <= 64 and w["n_base"] <= 2048) else
-                         ("k_ma_only<%d>" % (32 if w["n_hist"] >= 512 else 16 if w["n_hist"] >= 160 else 8)),
+                         "kernel": kernel,
                          "kernel_ms": main_ms_max / args.steps},
             "verdict_histogram_first_64k": hist_v,
         }
