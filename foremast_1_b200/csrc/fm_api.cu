@@ -376,7 +376,9 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
 int32_t fm_ctx_destroy(fm_ctx* c) {
   if (!c) return FM_OK;
   cudaSetDevice(c->device);
+  if (c->s_h2d) cudaStreamSynchronize(c->s_h2d);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->s_d2h) cudaStreamSynchronize(c->s_d2h);
   for (int i = 0; i < 2; ++i) {
     c->in[i].release(); c->out[i].release();
     if (c->in_ready[i]) cudaEventDestroy(c->in_ready[i]);
@@ -749,7 +751,7 @@ int32_t fm_rank_dump(fm_ctx* c, const float* cur, uint32_t n_cur, const float* b
   const uint32_t N = n_cur + n_base;
   if (N == 0) return FM_OK;
   if (!r2_out || (n_cur && !cur) || (n_base && !base)) return fail(c, FM_E_INVALID, "null pointer");
-  if (N > (1u << 20)) return fail(c, FM_E_UNSUPPORTED, "rank dump limited to 2^20 points");
+  if (N > (1u << 16)) return fail(c, FM_E_UNSUPPORTED, "rank dump is a parity aid, limited to 65536 points");
   FM_CK(c, cudaSetDevice(c->device));
   const uint32_t cap = pow2_ceil(N, 64u);
   auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
