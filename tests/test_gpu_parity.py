@@ -303,6 +303,32 @@ def test_errors(ctx):
     with pytest.raises(ForemastCudaError) as e:
         ctx.set_params(g2, t)
     assert e.value.code == A.FM_E_INVALID
+    # layout contract: struct_size, 16-byte alignment, pitch a multiple of 4 and >= roundup4(n)
+    import ctypes as C
+    lib = ctx._lib
+    cur = np.zeros((2, 8), np.float32)
+    rec = np.zeros(2, A.SERIES_REC)
+    b = A.Batch()
+    b.struct_size = C.sizeof(A.Batch) - 8
+    b.n_series, b.cur, b.n_cur, b.cur_pitch = 2, cur.ctypes.data, 8, 8
+    assert lib.fm_score_batch(ctx._h, C.byref(b), rec.ctypes.data, None, None, None, None) == A.FM_E_INVALID
+    assert b"struct_size" in lib.fm_last_error(ctx._h)
+    b.struct_size = C.sizeof(A.Batch)
+    b.cur_pitch = 6
+    assert lib.fm_score_batch(ctx._h, C.byref(b), rec.ctypes.data, None, None, None, None) == A.FM_E_INVALID
+    b.cur_pitch = 8
+    b.cur = cur.ctypes.data + 4
+    assert lib.fm_score_batch(ctx._h, C.byref(b), rec.ctypes.data, None, None, None, None) == A.FM_E_INVALID
+    b.cur = cur.ctypes.data
+    b.strategy = 7
+    assert lib.fm_score_batch(ctx._h, C.byref(b), rec.ctypes.data, None, None, None, None) == A.FM_E_INVALID
+    b.strategy = A.FM_STRAT_HISTORICAL
+    assert lib.fm_score_batch(ctx._h, C.byref(b), None, None, None, None, None) == A.FM_E_INVALID
+    # a batch without history is legal: every series is "unknown" (no model), not an error
+    assert lib.fm_score_batch(ctx._h, C.byref(b), rec.ctypes.data, None, None, None, None) == A.FM_OK
+    assert (rec["verdict"] == A.FM_UNKNOWN).all() and (rec["status"] & A.FM_ST_HIST_INSUFFICIENT).all()
+    b.n_series = 0
+    assert lib.fm_score_batch(ctx._h, C.byref(b), rec.ctypes.data, None, None, None, None) == A.FM_OK
     # the ctx stays usable after an error
     ctx.set_params(g, t)
     out = ctx.score(np.ones((1, 8), np.float32), np.ones((1, 16), np.float32))
