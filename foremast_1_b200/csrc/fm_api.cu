@@ -89,7 +89,7 @@ uint32_t round4(uint32_t n) { return (n + 3u) & ~3u; }
 bool mode_has(uint32_t mode, uint32_t t) { return mode == t || mode == FM_PW_ALL || mode == FM_PW_ANY; }
 
 // kind: 0 = k_score_series (generic), 2 = k_canary_sort<regs>, 3 = k_canary_elect<regs>, 4 = k_ma_only<regs>
-struct Plan { FmKArgs a; int wpc; int grid; bool fast; int kind; int regs; };
+struct Plan { FmKArgs a; int wpc; int grid; bool fast; int kind; int regs; int valid; };
 
 void fill_common(fm_ctx* c, const fm_batch* b, bool canary, FmKArgs& a) {
   a.cur = b->cur; a.cur_len = b->cur_len; a.n_cur = b->n_cur; a.cur_pitch = b->cur_pitch;
@@ -165,6 +165,7 @@ int32_t plan_canary_sort(fm_ctx* c, const fm_batch* b, Plan* pl) {
   if (!c->sort_smem_set) { FM_CK(c, fm_canary_sort_smem_attr((int)limit)); c->sort_smem_set = 1; }
   fill_common(c, b, true, a);
   pl->fast = true; pl->kind = 2; pl->regs = R;
+  pl->valid = (b->n_base <= 24u * (uint32_t)R) ? 3 * R / 4 : R;     // registers per lane that can hold keys
   return FM_OK;
 }
 
@@ -245,7 +246,7 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
 int launch_plan(const Plan& pl, cudaStream_t st) {
   if (pl.kind == 4) return fm_launch_ma_only(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 3) return fm_launch_canary_elect(pl.a, pl.regs, pl.grid, st);
-  if (pl.kind == 2) return fm_launch_canary_sort(pl.a, pl.regs, pl.wpc, pl.grid, st);
+  if (pl.kind == 2) return fm_launch_canary_sort(pl.a, pl.regs, pl.valid, pl.wpc, pl.grid, st);
   return fm_launch_score(pl.a, pl.wpc, pl.grid, st);
 }
 

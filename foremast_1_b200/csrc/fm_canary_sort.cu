@@ -28,7 +28,7 @@
 namespace {
 using namespace fmc;
 
-template <int R>
+template <int R, int RV>
 __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31;
@@ -89,7 +89,10 @@ __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
     FmMom mom = {0.0, 0.0};
     if (ranks || fuse_model) {
 #pragma unroll
-      for (int c = 0; c < R / 4; ++c) {
+      for (int c = RV / 4; c < R / 4; ++c)
+        v[4 * c + 0] = v[4 * c + 1] = v[4 * c + 2] = v[4 * c + 3] = CUDART_INF_F;
+#pragma unroll
+      for (int c = 0; c < RV / 4; ++c) {
         const uint32_t e0 = ((uint32_t)lane + 32u * c) << 2;
         float4 q = make_float4(CUDART_INF_F, CUDART_INF_F, CUDART_INF_F, CUDART_INF_F);
         if (e0 < nb) q = fm_lds_v4(base_s + (e0 << 2));
@@ -143,7 +146,7 @@ __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
     // ---- Mann-Whitney / Kruskal: sort the baseline in registers -------------------------------
     Prep t_mw = {false, false, 0.0, 0.0}, t_kw = {false, false, 0.0, 0.0};
     if (ranks) {
-      sort_rows<R>(v, lane);
+      sort_rows<R, RV>(v, lane);
 
       unsigned long long T = tie_term_and_park<R>(v, nb, lane, park_s);
 
@@ -177,17 +180,34 @@ __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
 
 }  // namespace
 
+template <int R, int RV>
+cudaError_t smem_attr(int bytes) {
+  return cudaFuncSetAttribute(k_canary_sort<R, RV>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
 cudaError_t fm_canary_sort_smem_attr(int bytes) {
-  cudaError_t e = cudaFuncSetAttribute(k_canary_sort<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_canary_sort<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_canary_sort<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  cudaError_t e = smem_attr<16, 12>(bytes);
+  if (e == cudaSuccess) e = smem_attr<16, 16>(bytes);
+  if (e == cudaSuccess) e = smem_attr<32, 24>(bytes);
+  if (e == cudaSuccess) e = smem_attr<32, 32>(bytes);
+  if (e == cudaSuccess) e = smem_attr<64, 48>(bytes);
+  if (e == cudaSuccess) e = smem_attr<64, 64>(bytes);
   return e;
 }
 
-int fm_launch_canary_sort(const FmKArgs& a, int regs, int warps_per_cta, int grid, cudaStream_t st) {
+int fm_launch_canary_sort(const FmKArgs& a, int regs, int valid_regs, int warps_per_cta, int grid, cudaStream_t st) {
   const size_t smem = (size_t)warps_per_cta * a.warp_bytes;
-  if (regs == 16) k_canary_sort<16><<<grid, warps_per_cta * 32, smem, st>>>(a);
-  else if (regs == 32) k_canary_sort<32><<<grid, warps_per_cta * 32, smem, st>>>(a);
-  else k_canary_sort<64><<<grid, warps_per_cta * 32, smem, st>>>(a);
+  const dim3 block(warps_per_cta * 32);
+  const bool part = valid_regs < regs;
+  if (regs == 16) {
+    if (part) k_canary_sort<16, 12><<<grid, block, smem, st>>>(a);
+    else k_canary_sort<16, 16><<<grid, block, smem, st>>>(a);
+  } else if (regs == 32) {
+    if (part) k_canary_sort<32, 24><<<grid, block, smem, st>>>(a);
+    else k_canary_sort<32, 32><<<grid, block, smem, st>>>(a);
+  } else {
+    if (part) k_canary_sort<64, 48><<<grid, block, smem, st>>>(a);
+    else k_canary_sort<64, 64><<<grid, block, smem, st>>>(a);
+  }
   return 1;
 }

@@ -55,7 +55,7 @@ struct FmGArgs {
 // launchers (fm_kernels.cu); each returns the number of kernels launched
 int fm_launch_score(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st);
 int fm_launch_groups(const FmGArgs& a, int warps_per_cta, int grid, cudaStream_t st);
-int fm_launch_canary_sort(const FmKArgs& a, int regs, int warps_per_cta, int grid, cudaStream_t st);
+int fm_launch_canary_sort(const FmKArgs& a, int regs, int valid_regs, int warps_per_cta, int grid, cudaStream_t st);
 cudaError_t fm_canary_sort_smem_attr(int bytes);
 int fm_launch_canary_elect(const FmKArgs& a, int nv, int grid, cudaStream_t st);
 size_t fm_canary_elect_fixed_bytes();

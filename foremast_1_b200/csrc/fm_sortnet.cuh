@@ -9,24 +9,96 @@
 namespace fmc {
 
 // ---- 32*R keys, R per lane, blocked: key index = R*lane + r --------------------------------
-// Bitonic sort in its all-ascending form: phase K first compares i with i ^ (K-1) ("flip"), then
-// i with i ^ J for J = K/4 .. 1; the lower index always keeps the minimum, so every lane-local
-// stage is a fixed pair of FMNMX on fixed registers (no per-lane direction to select on).
-// Template recursion over (K, J) keeps every register index a compile-time constant (a rolled
-// loop would push v[] to local memory).
+// Phase 1 sorts the R keys of every lane with Batcher's odd-even merge sort (543 comparators for
+// R = 64 against 672 of the bitonic network); registers >= RV are known to hold +inf padding and
+// the comparators that touch them are dropped at compile time (384 left for RV = 48).
+// The merge phases are bitonic in the all-ascending form: phase K first compares i with
+// i ^ (K-1) ("flip"), then i with i ^ J for J = K/4 .. 1; the lower index always keeps the
+// minimum, so every lane-local stage is a fixed pair of FMNMX on fixed registers.
+// Stages that cross lanes need min in one lane and max in its partner; ptxas turns a per-lane
+// choice into TWO predicated FMNMX per key (the ALU pipe is the bound of this kernel), so those
+// stages run on sign-folded keys instead: a lane whose direction bit is set holds -key, receives
+// its partner's folded key p and keeps min(w, -p) = -max(key, partner key) -- one FMNMX with a
+// free operand negation for both roles.  Moving between the conventions of two stages is one
+// FMUL by +-1 per key (exact; it issues on the otherwise idle FMA pipe).
+// Template recursion keeps every register index a compile-time constant (a rolled loop would
+// push v[] to local memory).
+template <int R, int RV, int I, int J>
+__device__ __forceinline__ void sort_ce(float (&v)[R]) {
+  if constexpr (J < RV) {
+    const float x = v[I], y = v[J];
+    v[I] = fminf(x, y);
+    v[J] = fmaxf(x, y);
+  }
+}
+template <int R, int RV, int I, int END, int DIST, int STEP>
+struct OemRow {
+  static __device__ __forceinline__ void run(float (&v)[R]) {
+    if constexpr (I + DIST < END) {
+      sort_ce<R, RV, I, I + DIST>(v);
+      OemRow<R, RV, I + STEP, END, DIST, STEP>::run(v);
+    }
+  }
+};
+template <int R, int RV, int LO, int N, int DIST>
+struct OemMerge {
+  static __device__ __forceinline__ void run(float (&v)[R]) {
+    if constexpr (2 * DIST < N) {
+      OemMerge<R, RV, LO, N, 2 * DIST>::run(v);
+      OemMerge<R, RV, LO + DIST, N, 2 * DIST>::run(v);
+      OemRow<R, RV, LO + DIST, LO + N, DIST, 2 * DIST>::run(v);
+    } else {
+      sort_ce<R, RV, LO, LO + DIST>(v);
+    }
+  }
+};
+template <int R, int RV, int LO, int N>
+struct OemSort {
+  static __device__ __forceinline__ void run(float (&v)[R]) {
+    if constexpr (N > 1 && LO < RV) {
+      OemSort<R, RV, LO, N / 2>::run(v);
+      OemSort<R, RV, LO + N / 2, N / 2>::run(v);
+      OemMerge<R, RV, LO, N, 1>::run(v);
+    }
+  }
+};
+
+__device__ __forceinline__ float sort_sign(int lane, int bit) { return (lane & bit) ? -1.0f : 1.0f; }
+
+// lane-crossing stages of phase K (K > R): direction bits K/2R, K/4R, .., 1
+template <int R, int BIT>
+struct SortCross {
+  static __device__ __forceinline__ void run(float (&v)[R], int lane) {
+    if constexpr (BIT >= 1) {
+      const float c = sort_sign(lane, BIT * 2) * sort_sign(lane, BIT);   // previous -> this convention
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float w = v[r] * c;
+        v[r] = fminf(w, -__shfl_xor_sync(FM_FULL, w, BIT));
+      }
+      SortCross<R, BIT / 2>::run(v, lane);
+    } else {
+      const float c = sort_sign(lane, 1);                                // back to plain keys
+#pragma unroll
+      for (int r = 0; r < R; ++r) v[r] *= c;
+    }
+  }
+};
 template <int R, int K>
 __device__ __forceinline__ void sort_flip(float (&v)[R], int lane) {
   if constexpr (K > R) {
     // partner: lane ^ (K/R - 1), register R-1-r.  Pairs (r, R-1-r) are exchanged together so that
     // both shuffles read values from before this stage.
-    const bool take_min = ((lane * R) & (K / 2)) == 0;
+    const float c = sort_sign(lane, K / (2 * R));
 #pragma unroll
     for (int r = 0; r < R / 2; ++r) {
-      const float o1 = __shfl_xor_sync(FM_FULL, v[R - 1 - r], K / R - 1);
-      const float o2 = __shfl_xor_sync(FM_FULL, v[r], K / R - 1);
-      v[r] = take_min ? fminf(v[r], o1) : fmaxf(v[r], o1);
-      v[R - 1 - r] = take_min ? fminf(v[R - 1 - r], o2) : fmaxf(v[R - 1 - r], o2);
+      const float wa = v[r] * c, wb = v[R - 1 - r] * c;
+      const float o1 = __shfl_xor_sync(FM_FULL, wb, K / R - 1);
+      const float o2 = __shfl_xor_sync(FM_FULL, wa, K / R - 1);
+      v[r] = fminf(wa, -o1);
+      v[R - 1 - r] = fminf(wb, -o2);
     }
+    SortCross<R, K / (4 * R)>::run(v, lane);
   } else {
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -39,41 +111,32 @@ __device__ __forceinline__ void sort_flip(float (&v)[R], int lane) {
   }
 }
 template <int R, int J>
-__device__ __forceinline__ void sort_disperse(float (&v)[R], int lane) {
-  if constexpr (J >= R) {
-    const bool take_min = ((lane * R) & J) == 0;
+__device__ __forceinline__ void sort_disperse(float (&v)[R]) {
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const float o = __shfl_xor_sync(FM_FULL, v[r], J / R);
-      v[r] = take_min ? fminf(v[r], o) : fmaxf(v[r], o);
-    }
-  } else {
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      if ((r & J) == 0) {
-        const float x = v[r], y = v[r | J];
-        v[r] = fminf(x, y);
-        v[r | J] = fmaxf(x, y);
-      }
+  for (int r = 0; r < R; ++r) {
+    if ((r & J) == 0) {
+      const float x = v[r], y = v[r | J];
+      v[r] = fminf(x, y);
+      v[r | J] = fmaxf(x, y);
     }
   }
 }
 template <int R, int J>
-struct SortMerge {
-  static __device__ __forceinline__ void run(float (&v)[R], int lane) {
-    sort_disperse<R, J>(v, lane);
-    SortMerge<R, J / 2>::run(v, lane);
+struct SortMerge {                       // lane-local strides J, J/2, .., 1
+  static __device__ __forceinline__ void run(float (&v)[R]) {
+    sort_disperse<R, J>(v);
+    SortMerge<R, J / 2>::run(v);
   }
 };
 template <int R>
 struct SortMerge<R, 0> {
-  static __device__ __forceinline__ void run(float (&)[R], int) {}
+  static __device__ __forceinline__ void run(float (&)[R]) {}
 };
 template <int R, int K, bool Done>
 struct SortPhase {
   static __device__ __forceinline__ void run(float (&v)[R], int lane) {
-    sort_flip<R, K>(v, lane);
-    SortMerge<R, K / 4>::run(v, lane);
+    sort_flip<R, K>(v, lane);            // K > R: includes the lane-crossing strides
+    SortMerge<R, (K / 4 < R ? K / 4 : R / 2)>::run(v);
     SortPhase<R, K * 2, (K * 2 > 32 * R)>::run(v, lane);
   }
 };
@@ -81,33 +144,43 @@ template <int R, int K>
 struct SortPhase<R, K, true> {
   static __device__ __forceinline__ void run(float (&)[R], int) {}
 };
-template <int R>
+// RV: registers [RV, R) of every lane hold +inf on entry
+template <int R, int RV = R>
 __device__ __forceinline__ void sort_rows(float (&v)[R], int lane) {
-  SortPhase<R, 2, false>::run(v, lane);
+  OemSort<R, RV, 0, R>::run(v);
+  SortPhase<R, 2 * R, false>::run(v, lane);
 }
 
-// transposed parking of the sorted row: key index i = R*lane + r lives at word r*32 + lane
+// transposed parking of the sorted row: key index i = R*lane + r lives at word r*32 + lane, every
+// word of the 32*R block is written (padding = +inf), so the bound searches are branch-free: five
+// steps over the lane minima (words 0..31), then log2(R) steps down that lane's column.
 template <int R>
 __device__ __forceinline__ uint32_t park_addr(uint32_t base_s, uint32_t i) {
   return base_s + (((i & (R - 1)) << 5) + (i / R)) * 4u;
 }
+template <int R, bool UPPER>
+__device__ __forceinline__ uint32_t parked_bound(uint32_t base_s, uint32_t n, float x) {
+  // pred(key) = key < x (lower bound) or key <= x (upper bound); count of keys with pred true
+  auto pred = [x](float k) { return UPPER ? !(x < k) : (k < x); };
+  const bool any = pred(fm_lds_f32(base_s));
+  uint32_t addr = base_s;                      // word (0, B): B = last lane whose minimum passes
+#pragma unroll
+  for (int h = 16; h > 0; h >>= 1)
+    if (pred(fm_lds_f32(addr + 4u * h))) addr += 4u * h;
+  const uint32_t col = addr;
+#pragma unroll
+  for (int h = R / 2; h > 0; h >>= 1)          // last register of that lane that passes
+    if (pred(fm_lds_f32(addr + 128u * h))) addr += 128u * h;
+  const uint32_t cnt = ((col - base_s) >> 2) * R + ((addr - col) >> 7) + 1u;
+  return any ? min(cnt, n) : 0u;
+}
 template <int R>
 __device__ __forceinline__ uint32_t parked_lower(uint32_t base_s, uint32_t n, float x) {
-  uint32_t lo = 0, len = n;
-  while (len) {
-    const uint32_t h = len >> 1;
-    if (fm_lds_f32(park_addr<R>(base_s, lo + h)) < x) { lo += h + 1; len -= h + 1; } else len = h;
-  }
-  return lo;
+  return parked_bound<R, false>(base_s, n, x);
 }
 template <int R>
 __device__ __forceinline__ uint32_t parked_upper(uint32_t base_s, uint32_t n, float x) {
-  uint32_t lo = 0, len = n;
-  while (len) {
-    const uint32_t h = len >> 1;
-    if (!(x < fm_lds_f32(park_addr<R>(base_s, lo + h)))) { lo += h + 1; len -= h + 1; } else len = h;
-  }
-  return lo;
+  return parked_bound<R, true>(base_s, n, x);
 }
 
 
