@@ -144,7 +144,7 @@ int32_t plan_canary_sort(fm_ctx* c, const fm_batch* b, Plan* pl) {
   a.cur_cap = 64;
   a.base_cap = round4(b->n_base);
   a.n_stages = 1;
-  a.warp_bytes = (uint32_t)((16 + (size_t)(64 + a.base_cap) * 4 + (size_t)128 * R + 127) & ~size_t(127));
+  a.warp_bytes = (uint32_t)((16 + (size_t)(64 + a.base_cap) * 4 + (size_t)128 * (R + 1) + 127) & ~size_t(127));
   const size_t limit = c->smem_optin ? c->smem_optin : 232448;
   const size_t sm_total = 233472;
   // register budget: __launch_bounds__(256, 2) caps the kernel at 128 registers -> 16 warps per SM

@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
     // ---- Mann-Whitney / Kruskal: sort the baseline in registers -------------------------------
     Prep t_mw = {false, false, 0.0, 0.0}, t_kw = {false, false, 0.0, 0.0};
     if (ranks) {
-      sort_rows<R, RV>(v, lane);
+      sort_rows<R, RV>(v, lane, park_s);
 
       unsigned long long T = tie_term_and_park<R>(v, nb, lane, park_s);
 

@@ -107,6 +107,19 @@ __device__ __forceinline__ int fm_set_lt(float a, float b) {
   return r;
 }
 
+// 1.0f when a == b else 0.0f (one FSET)
+__device__ __forceinline__ float fm_setf_eq(float a, float b) {
+  float r;
+  asm("set.eq.f32.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+// a product the compiler may not turn into a select
+__device__ __forceinline__ float fm_fmul(float a, float b) {
+  float r;
+  asm("mul.rn.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+
 __device__ __forceinline__ float4 fm_ldg_stream(const float4* p) {
   float4 r;
   asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"

@@ -80,7 +80,7 @@ struct SortCross {
     } else {
       const float c = sort_sign(lane, 1);                                // back to plain keys
 #pragma unroll
-      for (int r = 0; r < R; ++r) v[r] *= c;
+      for (int r = 0; r < R; ++r) v[r] = fm_fmul(v[r], c);                // (a plain product becomes an FSEL)
     }
   }
 };
@@ -132,23 +132,68 @@ template <int R>
 struct SortMerge<R, 0> {
   static __device__ __forceinline__ void run(float (&)[R]) {}
 };
+// ---- lane-crossing strides through shared memory (R >= 32, phases K >= kSmemFactor*R) ---------
+// A phase with k lane-crossing strides costs 64(3k+1) issue slots per lane as shuffles.  From k = 4
+// on, the row goes through the warp's parking buffer twice instead: written blocked, read
+// STRIPED (key 32*q + lane in register q), where every stride >= 32 is a lane-local FMNMX pair,
+// then written striped and read blocked for the strides below 32.  The reversal of the upper
+// half of each K-block (the "flip") is folded into the striped read.  The buffer holds lane block
+// l at words (R+1)*l .. (R+1)*l + R-1: the odd pitch makes the blocked accesses conflict-free
+// (bank = l + r), the striped ones touch 32 consecutive words.
+// (A rolled loop over the phases -- classic alternating directions on sign-folded keys, ~1200
+// instructions of loop body -- was measured 40 % slower: the back edges defeat the sequential
+// instruction prefetch that this mostly straight-line kernel lives on.)
+#ifndef FM_SORT_SMEM_FACTOR
+#define FM_SORT_SMEM_FACTOR 16
+#endif
+template <int R>
+__device__ __forceinline__ constexpr uint32_t xp_word(int q) {          // word of key 32*q (lane 0)
+  return (uint32_t)((R + 1) * ((32 * q) / R) + (32 * q) % R);
+}
+template <int R, int K>
+__device__ __forceinline__ void sort_phase_smem(float (&v)[R], int lane, uint32_t buf_s) {
+  const uint32_t blk = buf_s + 4u * (uint32_t)(R + 1) * (uint32_t)lane;
+  const uint32_t fwd = buf_s + 4u * (uint32_t)lane, rev = buf_s + 4u * (uint32_t)(lane ^ 31);
+  __syncwarp();
+#pragma unroll
+  for (int r = 0; r < R; ++r) fm_sts_f32(blk + 4u * r, v[r]);
+  __syncwarp();
+#pragma unroll
+  for (int q = 0; q < R; ++q) {
+    if (q & (K / 64)) v[q] = fm_lds_f32(rev + 4u * xp_word<R>(q ^ (K / 64 - 1)));   // upper half: reversed
+    else v[q] = fm_lds_f32(fwd + 4u * xp_word<R>(q));
+  }
+  SortMerge<R, K / 64>::run(v);              // strides K/2 .. 32 = register distances K/64 .. 1
+  __syncwarp();
+#pragma unroll
+  for (int q = 0; q < R; ++q) fm_sts_f32(fwd + 4u * xp_word<R>(q), v[q]);
+  __syncwarp();
+#pragma unroll
+  for (int r = 0; r < R; ++r) v[r] = fm_lds_f32(blk + 4u * r);
+  SortMerge<R, 16>::run(v);                  // strides 16 .. 1
+}
+
 template <int R, int K, bool Done>
 struct SortPhase {
-  static __device__ __forceinline__ void run(float (&v)[R], int lane) {
-    sort_flip<R, K>(v, lane);            // K > R: includes the lane-crossing strides
-    SortMerge<R, (K / 4 < R ? K / 4 : R / 2)>::run(v);
-    SortPhase<R, K * 2, (K * 2 > 32 * R)>::run(v, lane);
+  static __device__ __forceinline__ void run(float (&v)[R], int lane, uint32_t buf_s) {
+    if constexpr (R >= 32 && K >= FM_SORT_SMEM_FACTOR * R) {
+      sort_phase_smem<R, K>(v, lane, buf_s);
+    } else {
+      sort_flip<R, K>(v, lane);          // K > R: includes the lane-crossing strides
+      SortMerge<R, R / 2>::run(v);
+    }
+    SortPhase<R, K * 2, (K * 2 > 32 * R)>::run(v, lane, buf_s);
   }
 };
 template <int R, int K>
 struct SortPhase<R, K, true> {
-  static __device__ __forceinline__ void run(float (&)[R], int) {}
+  static __device__ __forceinline__ void run(float (&)[R], int, uint32_t) {}
 };
-// RV: registers [RV, R) of every lane hold +inf on entry
+// RV: registers [RV, R) of every lane hold +inf on entry; buf_s: 32*(R+1) words of shared memory
 template <int R, int RV = R>
-__device__ __forceinline__ void sort_rows(float (&v)[R], int lane) {
+__device__ __forceinline__ void sort_rows(float (&v)[R], int lane, uint32_t buf_s) {
   OemSort<R, RV, 0, R>::run(v);
-  SortPhase<R, 2 * R, false>::run(v, lane);
+  SortPhase<R, 2 * R, false>::run(v, lane, buf_s);
 }
 
 // transposed parking of the sorted row: key index i = R*lane + r lives at word r*32 + lane, every
@@ -186,28 +231,29 @@ __device__ __forceinline__ uint32_t parked_upper(uint32_t base_s, uint32_t n, fl
 
 // Tie term sum(t^3 - t) of the first n keys of a row sorted by sort_rows (+inf padding sorts
 // last), and the row parked at `park_s`.  Returns this lane's part; callers warp-sum it.
+// The runs are counted over all 32*R keys without a validity test per key (one FSET on the ALU
+// pipe, three FMA-pipe operations per key: c = position inside the run, exact in fp32); the run of
+// +inf that the padding forms, together with any +inf in the data, is then replaced by the run
+// the data alone would have.
 template <int R>
 __device__ __forceinline__ unsigned long long tie_term_and_park(const float (&v)[R], uint32_t n, int lane,
                                                                  uint32_t park_s) {
-  // lane-local runs; position i = R*lane + r counts while i < n
   const uint32_t i0 = (uint32_t)lane * R;
-  const uint32_t nvalid = n > i0 ? min(n - i0, (uint32_t)R) : 0u;
-  uint32_t run = 1, acc = 0;                  // acc = sum of c(c+1), c = position inside the run
+  float c = 0.0f, a1 = 0.0f, a2 = 0.0f;       // a1 + a2 = sum of c(c+1)
 #pragma unroll
   for (int r = 1; r < R; ++r) {
-    const bool eq = (v[r] == v[r - 1]) && ((uint32_t)r < nvalid);
-    run = eq ? run + 1u : 1u;
-    acc += eq ? (run - 1u) * run : 0u;
+    const float eq = fm_setf_eq(v[r], v[r - 1]);
+    c = fmaf(c, eq, eq);                      // (c + 1) inside a run, 0 at its first key
+    a1 += c;
+    a2 = fmaf(c, c, a2);
   }
-  unsigned long long T = 3ull * acc;
+  const uint32_t run = (uint32_t)c + 1u;      // run at my last key
+  unsigned long long T = 3ull * (uint32_t)(a1 + a2);
   // runs that continue from the previous lane: cin = points of my first value held by earlier lanes
-  float vlast = v[0];
-#pragma unroll
-  for (int r = 1; r < R; ++r) vlast = ((uint32_t)r < nvalid) ? v[r] : vlast;
-  const float prev_last = __shfl_up_sync(FM_FULL, vlast, 1);
+  const float prev_last = __shfl_up_sync(FM_FULL, v[R - 1], 1);
   const uint32_t prev_tail = __shfl_up_sync(FM_FULL, run, 1);      // previous lane: run at its last key
   const bool prev_full = __shfl_up_sync(FM_FULL, (run == (uint32_t)R) ? 1 : 0, 1) != 0;
-  const bool link = lane > 0 && nvalid > 0 && prev_last == v[0];
+  const bool link = lane > 0 && prev_last == v[0];
   uint32_t cin = link ? prev_tail : 0u;
   bool cont = link && prev_full;               // previous lane is one single run: add its carry too
 #pragma unroll
@@ -217,14 +263,20 @@ __device__ __forceinline__ unsigned long long tie_term_and_park(const float (&v)
     if (lane >= o && cont) { cin += cu; cont = bu != 0; }
   }
   // park the sorted row (transposed: conflict-free) and correct my head run for the carry
+  __syncwarp();
 #pragma unroll
   for (int r = 0; r < R; ++r) fm_sts_f32(park_s + ((uint32_t)(r * 32 + lane) << 2), v[r]);
   __syncwarp();
   if (cin > 0) {
     // what lies beyond this lane is corrected by the lanes that hold it
-    const uint32_t hlen = min(parked_upper<R>(park_s, n, v[0]) - i0, nvalid);
-    const unsigned long long h = hlen, c = cin;
-    T += h * (3ull * c * (c + h));           // tie_gain(cin, hlen) - tie_gain(0, hlen)
+    const uint32_t hlen = min(parked_upper<R>(park_s, 32u * R, v[0]) - i0, (uint32_t)R);
+    const unsigned long long h = hlen, cc = cin;
+    T += h * (3ull * cc * (cc + h));         // tie_gain(cin, hlen) - tie_gain(0, hlen)
+  }
+  if (lane == 0) {
+    const unsigned long long m = 32u * R - parked_lower<R>(park_s, 32u * R, CUDART_INF_F);  // keys equal to +inf
+    const unsigned long long q = m - (32u * R - n);                                         // of them in the data
+    T += (q * q * q - q) - (m * m * m - m);   // modular: the warp sum is what counts
   }
   return T;
 }
