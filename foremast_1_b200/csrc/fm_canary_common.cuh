@@ -12,7 +12,6 @@
 namespace fmc {
 
 constexpr uint32_t kCur = 64;          // floats reserved for the current row at the start of a stage
-constexpr unsigned long long kAbsMask = 0x7FFFFFFFFFFFFFFFull;
 
 __device__ __forceinline__ uint32_t row_len(const uint32_t* len, uint64_t s, uint32_t n) {
   return len ? min(__ldg(len + s), n) : n;
@@ -47,10 +46,10 @@ __device__ __forceinline__ void sort64(float& a, float& b, int lane) {
     }
   }
 }
-// same network on 64-bit keys compared with the top bit (the sign of the difference) masked
+// same network on 64-bit keys (|d| << 1 | sign: equal keys are identical, so the side that keeps
+// the maximum may replace on equality and one comparison serves both roles)
 __device__ __forceinline__ void cex64(unsigned long long& v, unsigned long long o, bool take_min) {
-  const unsigned long long vm = v & kAbsMask, om = o & kAbsMask;
-  const bool repl = take_min ? (om < vm) : (vm < om);
+  const bool repl = (o < v) == take_min;
   v = repl ? o : v;
 }
 __device__ __forceinline__ void sort64_abs(unsigned long long& a, unsigned long long& b, int lane) {
@@ -109,24 +108,28 @@ struct Prep { bool run; bool degenerate; double stat; double arg; };   // p = mi
 // Phase 1 reads the rows (time order) from the stage; phase 2 needs no shared memory, so the
 // caller may hand the stage back to the TMA unit in between.
 struct WxKeys { unsigned long long ka, kb; uint32_t nz, n_pairs; };
+__device__ __forceinline__ unsigned long long wx_key(double d) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(d);
+  return (b << 1) | (b >> 63);
+}
 
 __device__ __forceinline__ WxKeys wilcoxon_load(const fm_global_params& g, uint32_t stage_s, uint32_t nc,
                                                 uint32_t nb, int lane) {
-  // key = |d| as an ordered 64-bit integer, bit 63 = (d < 0); zero differences and padding get
-  // the largest key so that they sort behind the n' used ones
-  WxKeys k = {kAbsMask, kAbsMask, 0u, min(nc, nb)};
+  // key = |d| as an ordered 64-bit integer shifted left by one, bit 0 = (d < 0); zero differences
+  // and padding get the largest key so that they sort behind the n' used ones
+  WxKeys k = {~0ull, ~0ull, 0u, min(nc, nb)};
   const uint32_t base_s = stage_s + kCur * 4u;
   const uint32_t oc = g.pair_rule == FM_PAIR_TAIL ? nc - k.n_pairs : 0u;
   const uint32_t ob = g.pair_rule == FM_PAIR_TAIL ? nb - k.n_pairs : 0u;
   if ((uint32_t)lane < k.n_pairs) {
     const double d = __dsub_rn((double)fm_lds_f32(stage_s + 4u * (oc + lane)),
                                (double)fm_lds_f32(base_s + 4u * (ob + lane)));
-    if (d != 0.0) k.ka = (unsigned long long)__double_as_longlong(d); else ++k.nz;
+    if (d != 0.0) k.ka = wx_key(d); else ++k.nz;
   }
   if ((uint32_t)lane + 32u < k.n_pairs) {
     const double d = __dsub_rn((double)fm_lds_f32(stage_s + 4u * (oc + lane + 32u)),
                                (double)fm_lds_f32(base_s + 4u * (ob + lane + 32u)));
-    if (d != 0.0) k.kb = (unsigned long long)__double_as_longlong(d); else ++k.nz;
+    if (d != 0.0) k.kb = wx_key(d); else ++k.nz;
   }
   return k;
 }
@@ -139,7 +142,7 @@ __device__ __forceinline__ Prep wilcoxon_stat(const fm_global_params& g, WxKeys 
   if (!(np >= g.min_wx && np > 0)) return t;
   unsigned long long ka = k.ka, kb = k.kb;
   sort64_abs(ka, kb, lane);
-  const unsigned long long ma = ka & kAbsMask, mb = kb & kAbsMask;
+  const unsigned long long ma = ka >> 1, mb = kb >> 1;
   const unsigned long long pa = __shfl_up_sync(FM_FULL, ma, 1);
   const unsigned long long last_a = __shfl_sync(FM_FULL, ma, 31);
   unsigned long long pb = __shfl_up_sync(FM_FULL, mb, 1);
@@ -149,12 +152,12 @@ __device__ __forceinline__ Prep wilcoxon_stat(const fm_global_params& g, WxKeys 
   long long wp = 0, wm = 0, T = 0;
   if ((uint32_t)lane < np) {
     const long long r2 = (long long)(lo_a + e_a + 1u), tt = (long long)(e_a - lo_a);
-    if (ka >> 63) wm += r2; else wp += r2;
+    if (ka & 1ull) wm += r2; else wp += r2;
     T += tt * tt - 1;
   }
   if ((uint32_t)lane + 32u < np) {
     const long long r2 = (long long)(lo_b + e_b + 1u), tt = (long long)(e_b - lo_b);
-    if (kb >> 63) wm += r2; else wp += r2;
+    if (kb & 1ull) wm += r2; else wp += r2;
     T += tt * tt - 1;
   }
   wp = fm_warp_sum(wp); wm = fm_warp_sum(wm); T = fm_warp_sum(T);

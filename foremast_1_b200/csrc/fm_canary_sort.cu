@@ -78,9 +78,10 @@ __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
     const float ca = (uint32_t)lane < nc ? craw_a + 0.0f : CUDART_INF_F;
     const float cb = (uint32_t)lane + 32u < nc ? craw_b + 0.0f : CUDART_INF_F;
 
-    // Wilcoxon differences (pairs need the baseline in time order)
-    WxKeys wxk = {kAbsMask, kAbsMask, 0u, 0u};
-    if (want_wx) wxk = wilcoxon_load(g, stage_s, nc, nb, lane);
+    // ---- Wilcoxon signed rank (A.4): pairs need the baseline in time order; done before the
+    // baseline row occupies the registers
+    Prep t_wx = {false, false, 0.0, 0.0};
+    if (want_wx) t_wx = wilcoxon_stat(g, wilcoxon_load(g, stage_s, nc, nb, lane), lane, ax);
 
     // baseline: vector c of lane = float4 #(lane + 32 c); any assignment of points to lanes will do
     // for a sort, this one is bank-conflict free.  Missing points are +inf and sort to the end.
@@ -138,10 +139,6 @@ __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
       if (lane == 0)
         issue_rows(a, stage, bar, sn, row_len(a.cur_len, sn, a.n_cur), row_len(a.base_len, sn, a.n_base));
     }
-
-    // ---- Wilcoxon signed rank (A.4) -----------------------------------------------------------
-    Prep t_wx = {false, false, 0.0, 0.0};
-    if (want_wx) t_wx = wilcoxon_stat(g, wxk, lane, ax);
 
     // ---- Mann-Whitney / Kruskal: sort the baseline in registers -------------------------------
     Prep t_mw = {false, false, 0.0, 0.0}, t_kw = {false, false, 0.0, 0.0};
