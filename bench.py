@@ -92,12 +92,15 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def measured_traffic(kernel, n_series):
-    """DRAM bytes of one launch from the committed ncu capture of that kernel (None if not captured)."""
+def measured_traffic(kernel, workload, n_series):
+    """DRAM bytes of one launch from the committed ncu capture of that kernel ON THAT WORKLOAD
+    (None if this combination was not captured)."""
     try:
         with open(os.path.join(ROOT, "profiles", "r01", "traffic.json")) as f:
             t = json.load(f).get(kernel)
-        return None if t is None else int(t["bytes_per_series"]) * int(n_series)
+        if t is None or t.get("workload") != workload:
+            return None
+        return int(t["bytes_per_series"]) * int(n_series)
     except Exception:
         return None
 
@@ -208,6 +211,13 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local)
+    numa_cpus = None
+    if world > 1:   # every rank next to its own GPU's PCIe root before any pinned buffer exists
+        from foremast_1_b200.shard import bind_host_to_gpu
+        pr = torch.cuda.get_device_properties(local)
+        if hasattr(pr, "pci_bus_id"):
+            numa_cpus = bind_host_to_gpu("%04x:%02x:%02x.0" % (getattr(pr, "pci_domain_id", 0), pr.pci_bus_id,
+                                                               getattr(pr, "pci_device_id", 0)))
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -333,10 +343,11 @@ def main():
         rec_bytes = rec_dtype.itemsize
         bps = algorithmic_bytes(w, rec_bytes)
         achieved = S * bps / (main_ms_max / args.steps / 1e3) / 1e9
-        kernel = (("k_canary_sort<%d>" % (16 if w["n_base"] <= 512 else 32 if w["n_base"] <= 1024 else 64))
+        sort_r = 16 if w["n_base"] <= 512 else 32 if w["n_base"] <= 1024 else 64
+        kernel = (("k_canary_sort<%d, %d>" % (sort_r, 3 * sort_r // 4 if w["n_base"] <= 24 * sort_r else sort_r))
                   if (w["canary"] and w["n_cur"] <= 64 and w["n_base"] <= 2048) else
                   ("k_ma_only<%d>" % (32 if w["n_hist"] >= 512 else 16 if w["n_hist"] >= 160 else 8)))
-        traffic = measured_traffic(kernel, S) if (args.n_hist < 0 and not args.mode) else None
+        traffic = measured_traffic(kernel, args.workload, S) if (args.n_hist < 0 and not args.mode) else None
         line = {
             "metric": "series scored/sec", "value": value, "unit": "series/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms_max / args.steps,
@@ -345,7 +356,8 @@ def main():
             "config": {"workload": w["desc"], "series_per_gpu": S, "n_cur": w["n_cur"], "n_base": w["n_base"],
                        "n_hist": w["n_hist"], "pairwise": w["mode"], "sharding": "by series id, no collective",
                        "l2": "inputs (%.1f GB/GPU) larger than L2" % (S * (bps - rec_bytes) / 1e9),
-                       "timing": "CUDA events on the library stream, per step, max over ranks"},
+                       "timing": "CUDA events on the library stream, per step, max over ranks",
+                       "host_numa_binding": (len(numa_cpus) if numa_cpus else 0)},
             "wall_ms_per_step": wall_ms / args.steps,
             "gpu_launches": int(launches),
             "clocks": clocks,

@@ -76,3 +76,28 @@ def test_two_ranks_equal_one_rank():
         assert p.exitcode == 0
     want = _score_range(0, n)
     assert got == want.tobytes()
+
+
+def test_bind_host_to_gpu_reads_sysfs(tmp_path):
+    """NUMA binding helper: parses local_cpulist, ignores boxes that do not say (numa_node = -1)."""
+    import os
+    from foremast_1_b200 import shard
+    assert shard._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    dev = tmp_path / "0000:1b:00.0"
+    dev.mkdir()
+    (dev / "numa_node").write_text("-1\n")
+    (dev / "local_cpulist").write_text("0-1\n")
+    before = os.sched_getaffinity(0)
+    assert shard.bind_host_to_gpu("0000:1B:00.0", sysfs=str(tmp_path)) is None
+    assert shard.bind_host_to_gpu("0000:ff:00.0", sysfs=str(tmp_path)) is None      # unknown device
+    (dev / "numa_node").write_text("0\n")
+    (dev / "local_cpulist").write_text(",".join(str(c) for c in sorted(before)) + "\n")
+    assert shard.bind_host_to_gpu("0000:1b:00.0", sysfs=str(tmp_path)) is None      # whole allowed set: no change
+    if len(before) > 1:
+        one = min(before)
+        (dev / "local_cpulist").write_text("%d\n" % one)
+        try:
+            assert shard.bind_host_to_gpu("0000:1b:00.0", sysfs=str(tmp_path)) == {one}
+            assert os.sched_getaffinity(0) == {one}
+        finally:
+            os.sched_setaffinity(0, before)
