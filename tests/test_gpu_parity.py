@@ -153,6 +153,29 @@ def test_shapes(ctx, nc, nb):
     both(ctx, g, t, cur, base, metric_type=rng.integers(0, 6, S).astype(np.uint8))
 
 
+@pytest.mark.parametrize("nb", [383, 384, 385, 512, 513, 768, 769, 1024, 1025, 1439, 1536, 1537, 2047, 2048])
+def test_sort_kernel_tiers(ctx, nb):
+    """Every (keys per lane, pruned registers) instantiation of the register-sort kernel and both
+    sides of each boundary, with ragged lengths, long tie runs that cross lanes, values equal to
+    the row maximum (next to the +inf padding) and current points tied with baseline points."""
+    rng = np.random.default_rng(nb)
+    S = 96
+    cur = rng.normal(100, 3, (S, 60)).astype(np.float32)
+    base = rng.normal(100, 3, (S, nb)).astype(np.float32)
+    base[:32] = np.round(base[:32])                      # ~20 distinct values: runs of 50-200 keys
+    cur[:32] = np.round(cur[:32])
+    base[32:48, : nb // 2] = base[32:48, :1]             # one value fills half of the row
+    cur[32:48, :30] = base[32:48, :1]
+    base[48:56] = np.maximum(base[48:56], 101.0)         # a long run AT the minimum
+    base[56:64] = np.minimum(base[56:64], 99.0)          # and at the maximum (beside the padding)
+    cur[56:64, ::2] = 99.0
+    bl = np.full(S, nb, np.uint32)
+    bl[64:] = rng.integers(1, nb + 1, S - 64)
+    bl[64:68] = [1, 2, min(nb, 33), nb - 1]
+    g, t = params(min_hist_points=1)
+    both(ctx, g, t, cur, base, base_len=bl, metric_type=rng.integers(0, 6, S).astype(np.uint8))
+
+
 def test_param_variants(ctx):
     d = synth_desc(3, 800, 60, 1440, 0)
     cur, base, _, mt = synth_host(d)
