@@ -678,7 +678,21 @@ int32_t fm_score_groups_device(fm_ctx* c, const fm_group_batch* b, fm_series_rec
   uint32_t launches = 0;
   if (d_svc) FM_CK(c, cudaMemsetAsync(d_svc, 0, b->n_services * sizeof(fm_rollup_rec), c->stream));
   if (timing) FM_CK(c, cudaEventRecord(c->ev_a, c->stream));
-  launches += fm_launch_groups(a, wpc, grid, c->stream);
+  if (b->n_cur <= 64 && c->force_path != 1) {
+    // register-sort kernel for services of <= 8 groups; the rest (listed by it) go to the general one
+    const size_t al_n = (b->n_services * 4 + 255) & ~size_t(255);
+    FM_CK(c, c->misc.reserve(al_n + 256));
+    uint32_t* d_list = static_cast<uint32_t*>(c->misc.p);
+    uint32_t* d_cnt = reinterpret_cast<uint32_t*>(static_cast<char*>(c->misc.p) + al_n);
+    FM_CK(c, cudaMemsetAsync(d_cnt, 0, 4, c->stream));
+    const uint64_t need = (b->n_services + 23) / 24;               // 24 warps per CTA, one CTA per SM
+    const int g_fast = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms, need));
+    launches += fm_launch_groups_sort(a, d_list, d_cnt, g_fast, c->stream);
+    a.list = d_list; a.list_n = d_cnt;
+    launches += fm_launch_groups(a, wpc, std::min(grid, c->num_sms), c->stream);
+  } else {
+    launches += fm_launch_groups(a, wpc, grid, c->stream);
+  }
   if (timing) FM_CK(c, cudaEventRecord(c->ev_m, c->stream));
   launches += fm_launch_rollup_finalize_one(d_svc, b->n_services, c->stream);
   FM_CK(c, cudaGetLastError());

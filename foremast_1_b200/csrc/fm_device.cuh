@@ -107,6 +107,9 @@ __device__ __forceinline__ int fm_set_lt(float a, float b) {
   return r;
 }
 
+__device__ __forceinline__ void fm_prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 // 1.0f when a == b else 0.0f (one FSET)
 __device__ __forceinline__ float fm_setf_eq(float a, float b) {
   float r;

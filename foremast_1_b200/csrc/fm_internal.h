@@ -47,6 +47,8 @@ struct FmGArgs {
   fm_series_rec* out;
   fm_rollup_rec* svc;      // optional
   const FmParamsDev* P;
+  const uint32_t* list;    // optional: work off list[0 .. *list_n) instead of all services
+  const uint32_t* list_n;
   uint32_t pool_cap;       // floats: pooled sample, sorted (power of two)
   uint32_t raw_cap;        // floats: pooled sample in group order
   uint32_t warp_bytes;
@@ -55,6 +57,8 @@ struct FmGArgs {
 // launchers (fm_kernels.cu); each returns the number of kernels launched
 int fm_launch_score(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st);
 int fm_launch_groups(const FmGArgs& a, int warps_per_cta, int grid, cudaStream_t st);
+// fm_groups.cu: services of <= 8 groups x <= 64 points; the others are appended to defer_list
+int fm_launch_groups_sort(const FmGArgs& a, uint32_t* defer_list, uint32_t* defer_n, int grid, cudaStream_t st);
 int fm_launch_canary_sort(const FmKArgs& a, int regs, int valid_regs, int warps_per_cta, int grid, cudaStream_t st);
 cudaError_t fm_canary_sort_smem_attr(int bytes);
 int fm_launch_canary_elect(const FmKArgs& a, int nv, int grid, cudaStream_t st);

@@ -261,7 +261,9 @@ __global__ void __launch_bounds__(512) k_score_groups(const FmGArgs a) {
   float* pool = raw + a.raw_cap;
   const fm_global_params& g = a.P->g;
 
-  for (uint64_t v = (uint64_t)blockIdx.x * wpc + warp; v < a.n_services; v += (uint64_t)gridDim.x * wpc) {
+  const uint64_t n_iter = a.list ? (uint64_t)*a.list_n : a.n_services;
+  for (uint64_t it = (uint64_t)blockIdx.x * wpc + warp; it < n_iter; it += (uint64_t)gridDim.x * wpc) {
+    const uint64_t v = a.list ? (uint64_t)a.list[it] : it;
     const uint32_t g0 = a.group_offsets[v], g1 = a.group_offsets[v + 1];
     const uint32_t K = g1 - g0;
     const uint32_t ty = a.metric_type ? a.metric_type[v] : 0u;

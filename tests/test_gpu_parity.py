@@ -269,6 +269,38 @@ def test_groups_kruskal(ctx):
     assert (out["rec"]["status"][off[1]] & A.FM_ST_PAIRWISE_SKIPPED)
 
 
+@pytest.mark.parametrize("n_cur", [12, 60, 64, 100])
+def test_groups_mixed_shapes(ctx, n_cur):
+    """Services of 1..16 groups in one batch (more than 8 groups go through the deferred list to the
+    general kernel), ragged group lengths incl. empty ones, continuous and heavily tied values,
+    no history for the model (hist = None is legal: bounds are then skipped)."""
+    rng = np.random.default_rng(1000 + n_cur)
+    V = 300
+    K = rng.integers(1, 17, V)
+    K[:4] = [1, 2, 8, 9]
+    off = np.concatenate([[0], np.cumsum(K)]).astype(np.uint32)
+    G = int(off[-1])
+    cur = rng.normal(50, 5, (G, n_cur)).astype(np.float32)
+    tied = rng.random(V) < 0.5
+    for v in np.nonzero(tied)[0]:
+        cur[off[v]:off[v + 1]] = rng.poisson(2.0, (K[v], n_cur)).astype(np.float32)
+    cur[off[5]:off[6]] = 7.0                           # one value everywhere: degenerate, p = 1
+    hist = rng.normal(50, 5, (V, 500)).astype(np.float32)
+    hist[tied] = rng.poisson(2.0, (int(tied.sum()), 500)).astype(np.float32)
+    cl = rng.integers(0, n_cur + 1, G).astype(np.uint32)
+    cl[rng.random(G) < 0.7] = n_cur
+    hl = rng.integers(0, 501, V).astype(np.uint32)
+    hl[rng.random(V) < 0.8] = 500
+    mt = rng.integers(0, 6, V).astype(np.uint8)
+    g, t = params(pairwise_mode=A.FM_PW_KRUSKAL)
+    ctx.set_params(g, t)
+    out = ctx.score_groups(cur, off, hist, cur_len=cl, hist_len=hl, metric_type=mt)
+    ora = O.score_groups(g, t, out["batch"], n_threads=8)
+    assert_records_match(out["rec"], ora["rec"], cur, cl, bound_masks(t, np.repeat(mt, K), G))
+    assert (out["svc"] == ora["svc"]).all()
+    assert (out["rec"]["status"] & A.FM_ST_KW_RUN).any()
+
+
 def test_rank_dump(ctx):
     rng = np.random.default_rng(2)
     for nc, nb in [(5, 9), (60, 1440), (64, 64), (1, 0), (0, 3)]:
