@@ -28,7 +28,7 @@ constexpr int kGroups = 8;        // groups held in registers
 constexpr int kR = 2 * kGroups;   // keys per lane
 constexpr uint32_t kSyncEvery = FM_GROUPS_SYNC;   // services between two CTA barriers (power of two)
 constexpr bool kSyncTwice = false;  // second barrier between the history stream and the rank stage
-constexpr int kWarps = 24;        // one CTA per SM: all its warps walk the code together
+constexpr int kWarps = 32;        // one CTA per SM: all its warps walk the code together
 
 __device__ __forceinline__ uint32_t row_len(const uint32_t* len, uint64_t s, uint32_t n) {
   return len ? min(__ldg(len + s), n) : n;
@@ -187,6 +187,10 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
 }  // namespace
 
 int fm_launch_groups_sort(const FmGArgs& a, uint32_t* defer_list, uint32_t* defer_n, int grid, cudaStream_t st) {
-  k_groups_sort<<<grid, kWarps * 32, kWarps * 32 * kR * 4, st>>>(a, defer_list, defer_n);
+  constexpr int smem = kWarps * 32 * kR * 4;
+  if (smem > 48 * 1024 &&
+      cudaFuncSetAttribute(k_groups_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+    return 0;   // the caller's cudaGetLastError() reports it
+  k_groups_sort<<<grid, kWarps * 32, smem, st>>>(a, defer_list, defer_n);
   return 1;
 }
