@@ -346,7 +346,7 @@ def main():
         sort_r = 16 if w["n_base"] <= 512 else 32 if w["n_base"] <= 1024 else 64
         kernel = (("k_canary_sort<%d, %d>" % (sort_r, 3 * sort_r // 4 if w["n_base"] <= 24 * sort_r else sort_r))
                   if (w["canary"] and w["n_cur"] <= 64 and w["n_base"] <= 2048) else
-                  ("k_ma_only<%d>" % (32 if w["n_hist"] >= 512 else 16 if w["n_hist"] >= 160 else 8)))
+                  ("k_ma_only<%d>" % (16 if w["n_hist"] >= 1200 else 8 if w["n_hist"] >= 200 else 4)))
         traffic = measured_traffic(kernel, args.workload, S) if (args.n_hist < 0 and not args.mode) else None
         line = {
             "metric": "series scored/sec", "value": value, "unit": "series/s", "n_gpus": world,

@@ -23,7 +23,7 @@ FM_ST_DEGENERATE = 0x80
 
 FM_STRAT_CANARY, FM_STRAT_HISTORICAL = 0, 1
 FM_MA_ALL, FM_MA_WINDOW, FM_MODEL_EWMA, FM_MODEL_DOUBLE_EXP = 0, 1, 2, 3
-FM_PW_NONE, FM_PW_MANN_WHITE, FM_PW_WILCOXON, FM_PW_KRUSKAL, FM_PW_ALL, FM_PW_ANY = range(6)
+FM_PW_NONE, FM_PW_MANN_WHITE, FM_PW_WILCOXON, FM_PW_KRUSKAL, FM_PW_ALL, FM_PW_ANY, FM_PW_FRIEDMAN = range(7)
 FM_PAIR_HEAD, FM_PAIR_TAIL = 0, 1
 FM_REC_FULL, FM_REC_COMPACT = 0, 1
 

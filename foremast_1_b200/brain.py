@@ -81,7 +81,8 @@ def format_config(d):
 
 
 _PAIRWISE = {"ALL": A.FM_PW_ALL, "ANY": A.FM_PW_ANY, "MANN_WHITE": A.FM_PW_MANN_WHITE,
-             "WILCOXON": A.FM_PW_WILCOXON, "KRUSKAL": A.FM_PW_KRUSKAL, "NONE": A.FM_PW_NONE}
+             "WILCOXON": A.FM_PW_WILCOXON, "KRUSKAL": A.FM_PW_KRUSKAL, "NONE": A.FM_PW_NONE,
+             "FRIEDMAN": A.FM_PW_FRIEDMAN}   # rollover (pod-group) jobs only
 _ALGORITHMS = {"moving_average_all": A.FM_MA_ALL, "moving_average": A.FM_MA_WINDOW,
                "exponential_smoothing": A.FM_MODEL_EWMA,
                "double_exponential_smoothing": A.FM_MODEL_DOUBLE_EXP}

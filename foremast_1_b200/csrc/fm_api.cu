@@ -173,7 +173,8 @@ int32_t plan_canary_sort(fm_ctx* c, const fm_batch* b, Plan* pl) {
 int32_t plan_ma_only(fm_ctx* c, const fm_batch* b, Plan* pl) {
   FmKArgs& a = pl->a;
   fill_common(c, b, false, a);
-  pl->regs = b->n_hist >= 512 ? 32 : (b->n_hist >= 160 ? 16 : 8);      // lanes per series
+  pl->regs = b->n_hist >= 1200 ? 16 : (b->n_hist >= 200 ? 8 : 4);      // lanes per series (profiles/r01/sweep_c5.md)
+  if (const char* e = getenv("FOREMAST_CUDA_MA_GROUP")) pl->regs = atoi(e);   // experiment
   const uint64_t per_warp = 32 / pl->regs;
   const uint64_t need = (b->n_series + per_warp * 8 - 1) / (per_warp * 8);   // 8 warps per CTA
   pl->wpc = 8;
@@ -404,7 +405,7 @@ int32_t fm_set_params(fm_ctx* c, const fm_global_params* g, const fm_type_params
   if (!c) return FM_E_INVALID;
   if (!g || !table || n_types == 0 || n_types > FM_MAX_TYPES) return fail(c, FM_E_INVALID, "bad params (n_types %u)", n_types);
   if (g->struct_size != sizeof(fm_global_params)) return fail(c, FM_E_INVALID, "fm_global_params.struct_size %u != %zu", g->struct_size, sizeof(fm_global_params));
-  if (g->ddof > 1 || g->ma_mode > FM_MODEL_DOUBLE_EXP || g->pairwise_mode > FM_PW_ANY || g->pair_rule > FM_PAIR_TAIL)
+  if (g->ddof > 1 || g->ma_mode > FM_MODEL_DOUBLE_EXP || g->pairwise_mode > FM_PW_FRIEDMAN || g->pair_rule > FM_PAIR_TAIL)
     return fail(c, FM_E_INVALID, "parameter out of range");
   FM_CK(c, cudaSetDevice(c->device));
   c->params.g = *g;

@@ -407,6 +407,38 @@ __device__ __forceinline__ FmTest fm_kruskal(double s, double N, long long T, ui
   return t;
 }
 
+// A.4b Friedman chi-square over K related samples of n points each (x[j * stride + i] = point i of
+// group j, global or shared memory): block i = the i-th point of every group, lanes own blocks
+// lane, lane + 32, ...; twice the midrank of a value inside its block and the tie term are exact
+// integers, the statistic follows in fp64.  Whole warp; result uniform.
+__device__ __forceinline__ FmTest fm_friedman(const float* x, uint64_t stride, uint32_t K, uint32_t n, int lane) {
+  FmTest t = {true, false, 0.0, 1.0};
+  long long ssq = 0, ties = 0;
+  for (uint32_t j = 0; j < K; ++j) {
+    long long r2 = 0;
+    for (uint32_t i = lane; i < n; i += 32) {
+      const float xj = x[j * stride + i];
+      int lt = 0, eq = 0;
+      for (uint32_t m = 0; m < K; ++m) {
+        const float xm = x[m * stride + i];
+        lt += xm < xj; eq += xm == xj;
+      }
+      r2 += 2 * lt + eq + 1;
+      ties += (long long)eq * eq - 1;
+    }
+    r2 = fm_warp_sum(r2);
+    ssq += r2 * r2;
+  }
+  ties = fm_warp_sum(ties);
+  const double dk = (double)K, dn = (double)n;
+  const double c = 1.0 - (double)ties / (dk * (dk * dk - 1.0) * dn);
+  if (!(c > 0.0)) { t.degenerate = true; return t; }
+  const double q0 = 12.0 / (dk * dn * (dk + 1.0)) * (0.25 * (double)ssq) - 3.0 * dn * (dk + 1.0);
+  t.stat = q0 / c;
+  t.p = fm_chi2_sf(t.stat, K - 1);
+  return t;
+}
+
 __device__ __forceinline__ bool fm_mode_has(uint32_t mode, uint32_t test) {
   return mode == test || mode == FM_PW_ALL || mode == FM_PW_ANY;
 }

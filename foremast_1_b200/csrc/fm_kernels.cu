@@ -279,6 +279,20 @@ __global__ void __launch_bounds__(512) k_score_groups(const FmGArgs a) {
     FmTest kw = {false, false, 0.0, 1.0};
     uint32_t status_kw = 0;
     bool differ = false;
+    if (g.pairwise_mode == FM_PW_FRIEDMAN) {
+      uint32_t n = K ? row_len(a.cur_len, g0, a.n_cur) : 0u;
+      bool eligible = K >= 3 && K <= FM_MAX_GROUPS && n >= g.min_kw && n > 0;
+      for (uint32_t k = 1; eligible && k < K; ++k)
+        if (row_len(a.cur_len, g0 + k, a.n_cur) != n) eligible = false;
+      if (eligible) {
+        kw = fm_friedman(a.cur + (uint64_t)g0 * a.cur_pitch, a.cur_pitch, K, n, lane);
+        status_kw |= FM_ST_KW_RUN;
+        if (kw.degenerate) status_kw |= FM_ST_DEGENERATE;
+        else differ = kw.p < g.alpha;
+      }
+      if (!(status_kw & FM_ST_KW_RUN) || kw.degenerate) status_kw |= FM_ST_PAIRWISE_SKIPPED;
+      if (differ) status_kw |= FM_ST_DIFFER;
+    }
     if (g.pairwise_mode != FM_PW_NONE && fm_mode_has(g.pairwise_mode, FM_PW_KRUSKAL)) {
       bool eligible = K >= 2 && K <= FM_MAX_GROUPS;
       uint32_t N = 0;

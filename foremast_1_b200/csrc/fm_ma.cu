@@ -2,15 +2,15 @@
 // window-length sweep of BASELINE.json configs[4]): historical model -> mean, sigma -> bounds ->
 // anomalous current points -> verdict -> roll-up.  Pure streaming, HBM-bound.
 //
-// A group of G lanes owns one series (G = 8, 16 or 32 by history length), so a warp works on
+// A group of G lanes owns one series (G = 4, 8 or 16 by history length), so a warp works on
 // 32/G series at a time: a 60-point history is two 128-bit loads per lane, and the per-series
 // bookkeeping (reduction, fp64 square root, record) is shared by 32/G series per instruction.
 // Rows are read once with coalesced ld.global.nc.L1::no_allocate.v4 (consecutive series are
 // consecutive rows, so a warp's groups read one contiguous span); the history loop is software
 // pipelined with eight 16-byte loads per lane in flight, and the current row is requested first
 // so that its latency hides under the moments.  No shared memory, no staging: nothing is reused.
-// Measured (1M series, 16-byte records, B200): 41 % of the measured HBM copy rate at 60 points,
-// 79 % at 480, 91 % at 1440, >100 % from 2880 on (profiles/r01/sweep_c5.md).
+// Measured (1M series, 16-byte records, B200): 51 % of the measured HBM copy rate at 60 points,
+// 76 % at 240, 94 % at 480, >100 % from 960 on (profiles/r01/sweep_c5.md).
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -167,7 +167,9 @@ __global__ void __launch_bounds__(256, 4) k_ma_only(const FmKArgs a) {
 }  // namespace
 
 int fm_launch_ma_only(const FmKArgs& a, int group, int grid, cudaStream_t st) {
-  if (group == 8) k_ma_only<8><<<grid, 256, 0, st>>>(a);
+  if (group == 2) k_ma_only<2><<<grid, 256, 0, st>>>(a);
+  else if (group == 4) k_ma_only<4><<<grid, 256, 0, st>>>(a);
+  else if (group == 8) k_ma_only<8><<<grid, 256, 0, st>>>(a);
   else if (group == 16) k_ma_only<16><<<grid, 256, 0, st>>>(a);
   else k_ma_only<32><<<grid, 256, 0, st>>>(a);
   return 1;

@@ -82,6 +82,9 @@ extern "C" {
 #define FM_PW_KRUSKAL    3u
 #define FM_PW_ALL        4u
 #define FM_PW_ANY        5u
+#define FM_PW_FRIEDMAN   6u  /* group batches only: Friedman chi-square over the pod groups as related
+                              * samples ("Fried manchi square (special case)", docs/guides/design.md:92);
+                              * not part of ALL / ANY; statistic and p-value are reported in h / p_h   */
 
 #define FM_PAIR_HEAD 0u
 #define FM_PAIR_TAIL 1u

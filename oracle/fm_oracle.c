@@ -487,6 +487,45 @@ static void* fmo_group_worker(void* arg) {
     /* Kruskal-Wallis over the K groups (README.md:34,38). */
     fmo_test kw; memset(&kw, 0, sizeof(kw)); kw.p = 1.0;
     uint32_t status_kw = 0; int differ = 0;
+    if (g->pairwise_mode == FM_PW_FRIEDMAN) {
+      /* Friedman chi-square (docs/guides/design.md:92), DESIGN.md 3 (A.4b): the K groups as related
+       * samples, block i = the i-th point of every group.  Needs K >= 3 groups of one common
+       * length n >= MIN_KRUSKAL_DATA_POINTS. */
+      uint32_t n = K ? fmo_len(b->cur_len, g0, b->n_cur) : 0;
+      int eligible = K >= 3 && K <= FM_MAX_GROUPS && n >= g->min_kw && n > 0;
+      for (uint32_t k = 1; eligible && k < K; ++k)
+        if (fmo_len(b->cur_len, g0 + k, b->n_cur) != n) eligible = 0;
+      if (eligible) {
+        int64_t ssq = 0, ties = 0;            /* sum_j (2 R_j)^2 and sum over blocks of sum t(t^2-1) */
+        int64_t r2[FM_MAX_GROUPS]; memset(r2, 0, sizeof(r2));
+        for (uint32_t i = 0; i < n; ++i) {
+          for (uint32_t a = 0; a < K; ++a) {
+            const float xa = b->cur[(uint64_t)(g0 + a) * b->cur_pitch + i];
+            int64_t lt = 0, eq = 0;
+            for (uint32_t c = 0; c < K; ++c) {
+              const float xc = b->cur[(uint64_t)(g0 + c) * b->cur_pitch + i];
+              lt += xc < xa; eq += xc == xa;
+            }
+            r2[a] += 2 * lt + eq + 1;         /* twice the midrank inside the block */
+            ties += eq * eq - 1;              /* every member of a tie group of t adds t^2 - 1 */
+          }
+        }
+        for (uint32_t a = 0; a < K; ++a) ssq += r2[a] * r2[a];
+        const double dk = (double)K, dn = (double)n;
+        const double c = 1.0 - (double)ties / (dk * (dk * dk - 1.0) * dn);
+        status_kw |= FM_ST_KW_RUN;
+        kw.run = 1;
+        if (!(c > 0.0)) { kw.degenerate = 1; status_kw |= FM_ST_DEGENERATE; }
+        else {
+          const double q0 = 12.0 / (dk * dn * (dk + 1.0)) * (0.25 * (double)ssq) - 3.0 * dn * (dk + 1.0);
+          kw.stat = q0 / c;
+          kw.p = fmo_chi2_sf(kw.stat, K - 1);
+          differ = kw.p < g->alpha;
+        }
+      }
+      if (!(status_kw & FM_ST_KW_RUN) || kw.degenerate) status_kw |= FM_ST_PAIRWISE_SKIPPED;
+      if (differ) status_kw |= FM_ST_DIFFER;
+    }
     if (fmo_mode_has(g->pairwise_mode, FM_PW_KRUSKAL) && g->pairwise_mode != FM_PW_NONE) {
       uint32_t ng[FM_MAX_GROUPS]; int64_t r2g[FM_MAX_GROUPS]; uint32_t N = 0; int eligible = K >= 2 && K <= FM_MAX_GROUPS;
       for (uint32_t k = 0; eligible && k < K; ++k) {

@@ -121,6 +121,38 @@ def score_groups(g, table, gbatch, n_threads=4):
     return {"rec": rec, "svc": svc}
 
 
+def score_groups_arrays(g, table, cur, group_offsets, hist, cur_len=None, hist_len=None, metric_type=None,
+                        n_threads=4):
+    """score_groups on plain numpy arrays (rows packed with pitch = padded width); returns (rec, svc)."""
+    off = np.ascontiguousarray(group_offsets, dtype=np.uint32)
+    V, G = len(off) - 1, int(off[-1])
+
+    def pack(m):
+        m = np.asarray(m, np.float32)
+        pitch = (m.shape[1] + 3) & ~3
+        out = np.zeros((m.shape[0], pitch), np.float32)
+        out[:, : m.shape[1]] = m
+        return out, m.shape[1], pitch
+    b = A.GroupBatch()
+    b.struct_size = C.sizeof(A.GroupBatch)
+    b.n_services, b.n_groups, b.group_offsets = V, G, off.ctypes.data
+    cm, b.n_cur, b.cur_pitch = pack(cur)
+    b.cur = cm.ctypes.data
+    keep = [off, cm]
+    if hist is not None:
+        hm, b.n_hist, b.hist_pitch = pack(hist)
+        b.hist = hm.ctypes.data
+        keep.append(hm)
+    for name, arr, dt in (("cur_len", cur_len, np.uint32), ("hist_len", hist_len, np.uint32),
+                          ("metric_type", metric_type, np.uint8)):
+        if arr is not None:
+            a = np.ascontiguousarray(arr, dtype=dt)
+            keep.append(a)
+            setattr(b, name, a.ctypes.data)
+    r = score_groups(g, table, b, n_threads)
+    return r["rec"], r["svc"]
+
+
 def bench_synth(g, table, desc, strategy, hist_is_base, n_threads):
     secs = C.c_double()
     chk = C.c_uint64()

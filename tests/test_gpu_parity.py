@@ -301,6 +301,46 @@ def test_groups_mixed_shapes(ctx, n_cur):
     assert (out["rec"]["status"] & A.FM_ST_KW_RUN).any()
 
 
+@pytest.mark.parametrize("n_cur", [20, 60, 100])
+def test_groups_friedman(ctx, n_cur):
+    """Friedman chi-square (docs/guides/design.md:92) on both rollover kernels: 3..16 groups, tied and
+    continuous blocks, services whose groups differ in length (not evaluated), a shifted group."""
+    rng = np.random.default_rng(2000 + n_cur)
+    V = 240
+    K = rng.integers(1, 17, V)
+    K[:5] = [1, 2, 3, 8, 9]
+    off = np.concatenate([[0], np.cumsum(K)]).astype(np.uint32)
+    G = int(off[-1])
+    cur = rng.normal(50, 5, (G, n_cur)).astype(np.float32)
+    for v in range(0, V, 2):
+        cur[off[v]:off[v + 1]] = rng.poisson(2.0, (K[v], n_cur)).astype(np.float32)
+    for v in range(5, V, 7):
+        cur[off[v]] += 4.0                                  # one pod group off: the test fires
+    cur[off[6]:off[7]] = 1.0                                # degenerate
+    hist = rng.normal(50, 5, (V, 300)).astype(np.float32)
+    cl = np.full(G, n_cur, np.uint32)
+    for v in range(10, V, 11):
+        cl[off[v]] = n_cur - 1                              # unequal lengths
+    mt = rng.integers(0, 6, V).astype(np.uint8)
+    g, t = params(pairwise_mode=A.FM_PW_FRIEDMAN)
+    ctx.set_params(g, t)
+    out = ctx.score_groups(cur, off, hist, cur_len=cl, metric_type=mt)
+    ora = O.score_groups(g, t, out["batch"], n_threads=8)
+    assert_records_match(out["rec"], ora["rec"], cur, cl, bound_masks(t, np.repeat(mt, K), G))
+    assert (out["svc"] == ora["svc"]).all()
+    st = out["rec"]["status"]
+    assert (st & A.FM_ST_KW_RUN).any() and (st & A.FM_ST_DIFFER).any() and (st & A.FM_ST_PAIRWISE_SKIPPED).any()
+
+
+def test_friedman_mode_on_series_batches_is_skipped(ctx):
+    """The series (canary) path has no related samples: FRIEDMAN there evaluates no test."""
+    d = synth_desc(3, 64, 60, 1440, 0)
+    cur, base, _, mt = synth_host(d)
+    g, t = params(pairwise_mode=A.FM_PW_FRIEDMAN)
+    out, _, _ = both(ctx, g, t, cur, base, metric_type=mt)
+    assert (out["rec"]["status"] & A.FM_ST_PAIRWISE_SKIPPED).all()
+
+
 def test_rank_dump(ctx):
     rng = np.random.default_rng(2)
     for nc, nb in [(5, 9), (60, 1440), (64, 64), (1, 0), (0, 3)]:

@@ -198,3 +198,37 @@ def test_golden_records():
         out = run_case(name)
         for k, v in out.items():
             assert v.tobytes() == z[f"{name}__{k}"].tobytes(), (name, k)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_friedman_vs_scipy(seed):
+    """Friedman chi-square of the group path (docs/guides/design.md:92) against
+    scipy.stats.friedmanchisquare on float64 copies: continuous and heavily tied blocks."""
+    rng = np.random.default_rng(seed)
+    V = 12
+    K = rng.integers(3, 17, V)
+    off = np.concatenate([[0], np.cumsum(K)]).astype(np.uint32)
+    G = int(off[-1])
+    n = 40
+    cur = rng.normal(10, 2, (G, n)).astype(np.float32)
+    for v in range(0, V, 2):
+        cur[off[v]:off[v + 1]] = rng.poisson(1.5, (K[v], n)).astype(np.float32)
+    cur[off[1]:off[2]] = 3.0                                   # every block fully tied: degenerate
+    cl = np.full(G, n, np.uint32)
+    cl[off[3]] = n - 1                                         # unequal lengths: not evaluated
+    g, t = A.default_params()
+    g.pairwise_mode = A.FM_PW_FRIEDMAN
+    rec, svc = O.score_groups_arrays(g, t, cur, off, None, cur_len=cl)
+    for v in range(V):
+        r = rec[off[v]]
+        if v == 3:
+            assert not (r["status"] & A.FM_ST_KW_RUN) and (r["status"] & A.FM_ST_PAIRWISE_SKIPPED)
+            continue
+        assert r["status"] & A.FM_ST_KW_RUN
+        if v == 1:
+            assert (r["status"] & A.FM_ST_DEGENERATE) and r["p_h"] == 1.0
+            continue
+        q, p = stats.friedmanchisquare(*[cur[off[v] + k].astype(np.float64) for k in range(K[v])])
+        assert r["h"] == pytest.approx(q, rel=1e-12, abs=1e-12)
+        assert r["p_h"] == pytest.approx(p, rel=1e-10, abs=1e-300)
+        assert bool(r["status"] & A.FM_ST_DIFFER) == (r["p_h"] < g.alpha)
