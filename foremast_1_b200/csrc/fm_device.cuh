@@ -235,32 +235,73 @@ __device__ __forceinline__ void fm_moments_any(const float* x, uint32_t n, uint3
   fm_moments_finish(m, pivot, n, ddof, mean, sigma);
 }
 
-// Exponential / double exponential smoothing (design.md:60-66): a sequential
-// recurrence, evaluated by one lane and broadcast.
+// Exponential / double exponential smoothing (design.md:60-66), A.2: centre = one-step-ahead
+// forecast after the last sample, sigma = RMS one-step forecast error.  The recurrence
+//   level' = (1-a)(level + trend) + a x,   trend' = (1-ab) trend - ab level + ab x
+// is linear and time-invariant in the state (level, trend), so the warp evaluates it as a scan:
+// lane l owns a contiguous chunk of steps, pass 1 runs the chunk from the zero state (response r)
+// and from the two unit states (the columns of M^len), a 5-step warp scan composes the affine maps
+// (P, r) into every lane's true start state, pass 2 re-runs the chunk from that state and sums the
+// squared forecast errors.  Same arithmetic as the sequential form up to fp64 rounding order.
+struct FmAffine { double p00, p01, p10, p11, r0, r1; };
+__device__ __forceinline__ FmAffine fm_affine_after(const FmAffine& first, const FmAffine& then) {
+  // then o first
+  FmAffine o;
+  o.p00 = then.p00 * first.p00 + then.p01 * first.p10;
+  o.p01 = then.p00 * first.p01 + then.p01 * first.p11;
+  o.p10 = then.p10 * first.p00 + then.p11 * first.p10;
+  o.p11 = then.p10 * first.p01 + then.p11 * first.p11;
+  o.r0 = then.p00 * first.r0 + then.p01 * first.r1 + then.r0;
+  o.r1 = then.p10 * first.r0 + then.p11 * first.r1 + then.r1;
+  return o;
+}
 __device__ __forceinline__ void fm_model_smoothing(const fm_global_params& g, const float* x,
                                                    uint32_t n, int lane, double& mean,
                                                    double& sigma) {
-  double mu = 0.0, sg = 0.0;
-  if (lane == 0) {
-    const double a = g.smooth_alpha, b = g.smooth_beta;
-    const bool dbl = g.ma_mode == FM_MODEL_DOUBLE_EXP;
-    double level = (double)x[0], trend = 0.0, sse = 0.0;
-    if (dbl && n > 1) trend = (double)x[1] - (double)x[0];
-    uint32_t m = 0;
-    for (uint32_t t = 1; t < n; ++t) {
-      const double f = __dadd_rn(level, dbl ? trend : 0.0);
-      const double e = __dsub_rn((double)x[t], f);
-      sse = __dadd_rn(sse, __dmul_rn(e, e));
-      ++m;
-      const double nl = __dadd_rn(f, __dmul_rn(a, e));
-      if (dbl) trend = __dadd_rn(trend, __dmul_rn(b, __dsub_rn(__dsub_rn(nl, level), trend)));
-      level = nl;
-    }
-    mu = __dadd_rn(level, dbl ? trend : 0.0);
-    sg = (m > g.ddof) ? sqrt(sse / (double)(m - g.ddof)) : 0.0;
+  const bool dbl = g.ma_mode == FM_MODEL_DOUBLE_EXP;
+  const double a = g.smooth_alpha, ab = dbl ? g.smooth_alpha * g.smooth_beta : 0.0;
+  const double m00 = 1.0 - a, m01 = 1.0 - a, m10 = -ab, m11 = 1.0 - ab;
+  const double level0 = (double)x[0], trend0 = (dbl && n > 1) ? (double)x[1] - (double)x[0] : 0.0;
+  const uint32_t steps = n - 1u;                         // t = 1 .. n-1
+  const uint32_t L = (steps + 31u) / 32u;
+  const uint32_t t0 = 1u + (uint32_t)lane * L, t1 = min(n, t0 + L);
+  // pass 1: zero-state response and M^len of my chunk
+  FmAffine me = {1.0, 0.0, 0.0, 1.0, 0.0, 0.0};
+  for (uint32_t t = t0; t < t1; ++t) {
+    const double xt = (double)x[t];
+    const double q00 = m00 * me.p00 + m01 * me.p10, q01 = m00 * me.p01 + m01 * me.p11;
+    const double q10 = m10 * me.p00 + m11 * me.p10, q11 = m10 * me.p01 + m11 * me.p11;
+    const double s0 = m00 * me.r0 + m01 * me.r1 + a * xt, s1 = m10 * me.r0 + m11 * me.r1 + ab * xt;
+    me.p00 = q00; me.p01 = q01; me.p10 = q10; me.p11 = q11; me.r0 = s0; me.r1 = s1;
   }
-  mean = __shfl_sync(FM_FULL, mu, 0);
-  sigma = __shfl_sync(FM_FULL, sg, 0);
+  // inclusive scan of the affine maps over the lanes
+  FmAffine inc = me;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    FmAffine up;
+    up.p00 = __shfl_up_sync(FM_FULL, inc.p00, o); up.p01 = __shfl_up_sync(FM_FULL, inc.p01, o);
+    up.p10 = __shfl_up_sync(FM_FULL, inc.p10, o); up.p11 = __shfl_up_sync(FM_FULL, inc.p11, o);
+    up.r0 = __shfl_up_sync(FM_FULL, inc.r0, o); up.r1 = __shfl_up_sync(FM_FULL, inc.r1, o);
+    if (lane >= o) inc = fm_affine_after(up, inc);
+  }
+  // state at the end of my chunk, and (from the lane before) at its start
+  const double end_l = inc.p00 * level0 + inc.p01 * trend0 + inc.r0;
+  const double end_t = inc.p10 * level0 + inc.p11 * trend0 + inc.r1;
+  double level = __shfl_up_sync(FM_FULL, end_l, 1), trend = __shfl_up_sync(FM_FULL, end_t, 1);
+  if (lane == 0) { level = level0; trend = trend0; }
+  // pass 2: forecast errors of my chunk from its true start state
+  double sse = 0.0;
+  for (uint32_t t = t0; t < t1; ++t) {
+    const double f = level + trend;
+    const double e = (double)x[t] - f;
+    sse = fma(e, e, sse);
+    const double nl = f + a * e;
+    trend = trend + (dbl ? g.smooth_beta : 0.0) * (nl - level - trend);
+    level = nl;
+  }
+  sse = fm_warp_sum(sse);
+  mean = __shfl_sync(FM_FULL, end_l, 31) + __shfl_sync(FM_FULL, end_t, 31);
+  sigma = (steps > g.ddof) ? sqrt(sse / (double)(steps - g.ddof)) : 0.0;
 }
 
 // a2: model window -> (mean, sigma).  `x` global or shared; `vec_ok` = row is a

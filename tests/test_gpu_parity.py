@@ -341,6 +341,26 @@ def test_friedman_mode_on_series_batches_is_skipped(ctx):
     assert (out["rec"]["status"] & A.FM_ST_PAIRWISE_SKIPPED).all()
 
 
+@pytest.mark.parametrize("mode", [A.FM_MODEL_EWMA, A.FM_MODEL_DOUBLE_EXP])
+@pytest.mark.parametrize("nh", [1, 2, 3, 31, 32, 33, 64, 100, 1440, 10080])
+def test_smoothing_models_scan(ctx, mode, nh):
+    """Exponential / double exponential smoothing evaluated as a warp scan of affine maps against
+    the oracle's sequential recurrence: every chunking edge (fewer steps than lanes, one step per
+    lane, ragged last chunk), ragged history lengths, trending and level-shifted rows."""
+    rng = np.random.default_rng(300 + nh)
+    S = 48
+    t = np.arange(nh, dtype=np.float64)
+    hist = (100 + 0.01 * t[None, :] * rng.normal(1, 0.5, (S, 1)) + rng.normal(0, 2, (S, nh))).astype(np.float32)
+    hist[: S // 4, nh // 2:] += 15.0
+    cur = (hist[:, -1:] + rng.normal(0, 3, (S, 30))).astype(np.float32)
+    hl = np.full(S, nh, np.uint32)
+    hl[S // 2:] = rng.integers(0, nh + 1, S - S // 2)
+    for al, be in ((0.3, 0.1), (0.9, 0.5), (0.05, 0.01)):
+        g, tb = params(ma_mode=mode, smooth_alpha=al, smooth_beta=be, min_hist_points=1, pairwise_mode=A.FM_PW_NONE)
+        both(ctx, g, tb, cur, None, hist, hist_len=hl, strategy=A.FM_STRAT_HISTORICAL,
+             metric_type=rng.integers(0, 6, S).astype(np.uint8))
+
+
 def test_rank_dump(ctx):
     rng = np.random.default_rng(2)
     for nc, nb in [(5, 9), (60, 1440), (64, 64), (1, 0), (0, 3)]:
