@@ -144,17 +144,23 @@ int32_t plan_canary_sort(fm_ctx* c, const fm_batch* b, Plan* pl) {
   a.cur_cap = 64;
   a.base_cap = round4(b->n_base);
   a.n_stages = 1;
-  a.warp_bytes = (uint32_t)((16 + (size_t)(64 + a.base_cap) * 4 + (size_t)128 * (R + 1) + 127) & ~size_t(127));
+  // 1025..1536 points: the padding-free 1536-key network (fm_sort48.cuh) needs a 6 KB buffer only.
+  // (18 warps per SM at 112 registers would fit then; measured 7.5 ms against 5.0: the spills meet
+  // an L1 that 221 KB of shared memory have shrunk to a few KB.)
+  const bool k48 = R == 64 && b->n_base <= 1536;
+  const size_t buf_bytes = k48 ? 6144 : (size_t)128 * (R + 1);
+  const int max_warps = 16;
+  a.warp_bytes = (uint32_t)((16 + (size_t)(64 + a.base_cap) * 4 + buf_bytes + 127) & ~size_t(127));
   const size_t limit = c->smem_optin ? c->smem_optin : 232448;
   const size_t sm_total = 233472;
   // register budget: __launch_bounds__(256, 2) caps the kernel at 128 registers -> 16 warps per SM
   // (measured: 16 warps with a few spilled registers beat 12 warps at 168 registers, 7.0 vs 8.1 ms)
   int best_w = 1, best_total = 0;
-  for (int w = 1; w <= 8; ++w) {
+  for (int w = 1; w <= max_warps / 2; ++w) {
     const size_t cta = (size_t)w * a.warp_bytes;
     if (cta > limit) break;
     int ctas = (int)(sm_total / (cta + 1024));
-    ctas = std::min(ctas, 16 / w);
+    ctas = std::min(ctas, max_warps / w);
     if (ctas < 1) continue;
     if (ctas * w >= best_total) { best_total = ctas * w; best_w = w; }
   }

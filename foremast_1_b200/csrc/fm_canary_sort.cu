@@ -24,6 +24,7 @@
 
 #include "fm_canary_common.cuh"
 #include "fm_sortnet.cuh"
+#include "fm_sort48.cuh"
 
 namespace {
 using namespace fmc;
@@ -85,12 +86,14 @@ __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
 
     // baseline: vector c of lane = float4 #(lane + 32 c); any assignment of points to lanes will do
     // for a sort, this one is bank-conflict free.  Missing points are +inf and sort to the end.
-    float v[R];
+    constexpr bool k48 = (R == 64 && RV == 48);      // 1536-key network without the padding (fm_sort48.cuh)
+    constexpr int NK = k48 ? 48 : R;
+    float v[NK];
     const double pivot = nb ? (double)fm_lds_f32(base_s) : 0.0;
     FmMom mom = {0.0, 0.0};
     if (ranks || fuse_model) {
 #pragma unroll
-      for (int c = RV / 4; c < R / 4; ++c)
+      for (int c = RV / 4; c < NK / 4; ++c)
         v[4 * c + 0] = v[4 * c + 1] = v[4 * c + 2] = v[4 * c + 3] = CUDART_INF_F;
 #pragma unroll
       for (int c = 0; c < RV / 4; ++c) {
@@ -143,9 +146,16 @@ __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
     // ---- Mann-Whitney / Kruskal: sort the baseline in registers -------------------------------
     Prep t_mw = {false, false, 0.0, 0.0}, t_kw = {false, false, 0.0, 0.0};
     if (ranks) {
-      sort_rows<R, RV>(v, lane, park_s);
-
-      unsigned long long T = tie_term_and_park<R>(v, nb, lane, park_s);
+      unsigned long long T;
+      if constexpr (k48) {
+        sort_rows48(v, lane, park_s);
+        T = tie_term_and_park48(v, nb, lane, park_s);
+      } else {
+        sort_rows<R, RV>(v, lane, park_s);
+        T = tie_term_and_park<R>(v, nb, lane, park_s);
+      }
+      auto lower = [&](float x) { if constexpr (k48) return parked48_bound<false>(park_s, nb, x); else return parked_lower<R>(park_s, nb, x); };
+      auto upper = [&](float x) { if constexpr (k48) return parked48_bound<true>(park_s, nb, x); else return parked_upper<R>(park_s, nb, x); };
 
       // current row: sorted for its own tie positions, each point located in the parked baseline
       float sa = ca, sb = cb;
@@ -154,13 +164,13 @@ __global__ void __launch_bounds__(256, 2) k_canary_sort(const FmKArgs a) {
       runs64f(sa, sb, lane, lo_a, lo_b, e_a, e_b);
       long long r2c = 0;
       if ((uint32_t)lane < nc) {
-        const uint32_t lb = parked_lower<R>(park_s, nb, sa), tb = parked_upper<R>(park_s, nb, sa) - lb;
+        const uint32_t lb = lower(sa), tb = upper(sa) - lb;
         const unsigned long long c = tb + ((uint32_t)lane - lo_a);
         r2c += 2ll * lb + tb;
         T += 3ull * c * (c + 1ull);
       }
       if ((uint32_t)lane + 32u < nc) {
-        const uint32_t lb = parked_lower<R>(park_s, nb, sb), tb = parked_upper<R>(park_s, nb, sb) - lb;
+        const uint32_t lb = lower(sb), tb = upper(sb) - lb;
         const unsigned long long c = tb + ((uint32_t)lane + 32u - lo_b);
         r2c += 2ll * lb + tb;
         T += 3ull * c * (c + 1ull);

@@ -72,6 +72,9 @@ __device__ __forceinline__ float4 fm_lds_v4(uint32_t a) {
                : "memory");
   return v;
 }
+__device__ __forceinline__ void fm_sts_v4(uint32_t a, float x, float y, float z, float w) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
 __device__ __forceinline__ void fm_sts_u32(uint32_t a, uint32_t v) {
   asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
 }
