@@ -310,6 +310,52 @@ class MemoryStore:
         return True
 
 
+class ElasticsearchStore:
+    """The same two operations against the 'documents' index of the Elasticsearch instance
+    foremast-service writes to (elasticsearchstore.go:16-19: index "documents", type "document";
+    search by status as in ByStatus, elasticsearchstore.go:124-149).
+
+    by_status   POST /documents/_search  {"query": {"terms": {"status": [...]}}, "size": limit}
+    update      POST /documents/document/<id>/_update with a script that applies the fields only
+                while modified_at still has the value the caller saw (the claim / takeover race
+                between brain workers); Elasticsearch answers "noop" when somebody else won.
+
+    `transport(method, url, body_dict) -> dict` defaults to urllib; tests inject a fake."""
+
+    def __init__(self, base_url, index="documents", doc_type="document", transport=None):
+        self.base = base_url.rstrip("/")
+        self.index, self.doc_type = index, doc_type
+        self.transport = transport or self._urllib
+
+    @staticmethod
+    def _urllib(method, url, body):
+        req = urllib.request.Request(url, data=json.dumps(body).encode(), method=method,
+                                     headers={"Content-Type": "application/json"})
+        with urllib.request.urlopen(req, timeout=30) as r:
+            return json.loads(r.read().decode())
+
+    def by_status(self, statuses, limit=1000):
+        body = {"query": {"terms": {"status": sorted(statuses)}}, "size": int(limit)}
+        res = self.transport("POST", f"{self.base}/{self.index}/_search", body)
+        out = []
+        for hit in res.get("hits", {}).get("hits", []):
+            d = dict(hit.get("_source", {}))
+            d.setdefault("id", hit.get("_id"))
+            out.append(d)
+        return out
+
+    def update(self, doc_id, expect_modified_at=None, **fields):
+        url = f"{self.base}/{self.index}/{self.doc_type}/{doc_id}/_update"
+        if expect_modified_at is None and "modified_at" not in fields:
+            res = self.transport("POST", url, {"doc": fields})
+        else:
+            script = ("if (params.expect == null || ctx._source.modified_at == params.expect) "
+                      "{ ctx._source.putAll(params.doc) } else { ctx.op = 'noop' }")
+            res = self.transport("POST", url, {"script": {"lang": "painless", "source": script,
+                                                          "params": {"expect": expect_modified_at, "doc": fields}}})
+        return res.get("result") != "noop"
+
+
 class BrainWorker:
     """Poll / claim / score / write-back loop (design.md:37-43).
 

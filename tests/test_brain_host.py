@@ -177,3 +177,35 @@ def test_worker_claim_takeover_and_fail_fast():
     assert "bad" not in res                       # completed documents are not re-scored
     # an optimistic-lock loser does not claim
     assert store.update("ok", expect_modified_at=-1.0, status="x") is False
+
+
+def test_elasticsearch_store_speaks_the_documents_index():
+    """ElasticsearchStore against a fake transport: search by status, optimistic update."""
+    from foremast_1_b200 import brain
+    docs = {"a1": {"status": "initial", "modified_at": 5.0, "appName": "x"},
+            "b2": {"status": "completed_health", "modified_at": 6.0}}
+    calls = []
+
+    def transport(method, url, body):
+        calls.append((method, url, body))
+        if url.endswith("/documents/_search"):
+            want = set(body["query"]["terms"]["status"])
+            hits = [{"_id": k, "_source": dict(v)} for k, v in docs.items() if v["status"] in want]
+            return {"hits": {"hits": hits[: body["size"]]}}
+        doc_id = url.split("/")[-2]
+        p = body["script"]["params"] if "script" in body else {"expect": None, "doc": body["doc"]}
+        if p["expect"] is not None and docs[doc_id]["modified_at"] != p["expect"]:
+            return {"result": "noop"}
+        docs[doc_id].update(p["doc"])
+        return {"result": "updated"}
+
+    st = brain.ElasticsearchStore("http://es:9200/", transport=transport)
+    got = st.by_status({"initial", "preprocess_inprogress"})
+    assert [d["id"] for d in got] == ["a1"] and got[0]["appName"] == "x"
+    assert calls[0][1] == "http://es:9200/documents/_search"
+    assert st.update("a1", expect_modified_at=5.0, status="preprocess_inprogress", modified_at=9.0)
+    assert docs["a1"]["status"] == "preprocess_inprogress"
+    assert not st.update("a1", expect_modified_at=5.0, status="initial", modified_at=10.0)   # lost the race
+    assert calls[-1][1] == "http://es:9200/documents/document/a1/_update"
+    assert st.update("b2", reason="ok")
+    assert docs["b2"]["reason"] == "ok"
