@@ -6,12 +6,12 @@
 //       pulled the rows into registers (conflict-free 128-bit LDS) it re-arms the same stage for
 //       its NEXT series, so the copy runs under the whole ranking of the current one.
 //   a2  pivoted fp64 moments from the registers, warp-shuffle reduction.
-//   a4  the baseline row is sorted IN REGISTERS by a bitonic network over the warp: R keys per
-//       lane (blocked), strides < R are lane-local FMNMX pairs, strides >= R one SHFL.BFLY + one
-//       predicated FMNMX per key.  Tie term from the run lengths (lane-local scan + a 5-step
-//       segmented warp scan for runs that cross lanes).  The sorted row is then parked in shared
-//       memory (transposed, conflict-free) and each current point finds its lower / upper bound
-//       there: 2*R1 = n1(n1+1) + sum(2*lb + (ub - lb)).
+//   a4  the baseline row is sorted IN REGISTERS by a network over the warp (fm_sortnet.cuh: odd-even
+//       merge sort per lane, bitonic merge phases with sign-folded shuffles or through the parking
+//       buffer; fm_sort48.cuh: the padding-free 1536-key network for 1025..1536 points).  Tie term
+//       from the run lengths (lane-local scan + a 5-step segmented warp scan for runs that cross
+//       lanes).  The sorted row is then parked in shared memory (conflict-free) and each current
+//       point finds its lower / upper bound there: 2*R1 = n1(n1+1) + sum(2*lb + (ub - lb)).
 //       Wilcoxon: 64 fp64 |differences| sorted across the warp, tie runs by warp scans.
 //   a5..a9  one erfc for the three p-values (lanes 0..2), decision, thresholds, anomaly ballot,
 //       fused roll-up atomics.
