@@ -34,6 +34,8 @@ SYMBOLS = {
     "fm_ma_window_series": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
     "fm_ma_window_series_static": (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
     "fm_synth_fill_device": (C.c_int32, [C.c_void_p, C.POINTER(A.SynthDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fm_decode_query_range": (C.c_int64, [C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
+                                          C.c_uint32, C.POINTER(C.c_uint32)]),
     "fm_synth_fill_host": (C.c_int32, [C.POINTER(A.SynthDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "fm_ctx_sync": (C.c_int32, [C.c_void_p]),
     "fm_last_error": (C.c_char_p, [C.c_void_p]),

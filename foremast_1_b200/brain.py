@@ -17,6 +17,7 @@ libforemast_cuda.so through engine.Context.
   BrainWorker           poll / claim / takeover loop over a document store
                         (pkg/search/elasticsearchstore.go:124-149; design.md:37-43)
 """
+import ctypes as C
 import json
 import time
 import urllib.request
@@ -173,6 +174,29 @@ def decode_query_range(payload):
         keep = np.isfinite(x)
         out.append((r.get("metric", {}), ts[keep], x[keep].astype(np.float32)))
     return out
+
+
+def decode_query_range_fast(body):
+    """Same result as decode_query_range for a raw response body (bytes), through the C scanner
+    fm_decode_query_range of libforemast_cuda.so: no Python objects per sample.  The labels are not
+    decoded ({} in their place): merge_series and the scoring path do not use them."""
+    from . import _ffi
+    if isinstance(body, str):
+        body = body.encode("utf-8")
+    body = bytes(body)
+    cap = len(body) // 8 + 1                      # a sample takes at least [0,"0"], = 8 bytes
+    cap_series = body.count(b'"value') + 2
+    ts = np.empty(cap, np.int64)
+    x = np.empty(cap, np.float32)
+    start = np.zeros(cap_series, np.uint32)
+    n_series = C.c_uint32(0)
+    n = _ffi.lib().fm_decode_query_range(body, len(body), ts.ctypes.data, x.ctypes.data, cap,
+                                         start.ctypes.data, cap_series, C.byref(n_series))
+    if n < 0:
+        msg = _ffi.lib().fm_last_error(None)
+        raise ValueError((msg or b"fm_decode_query_range failed").decode())
+    return [({}, ts[start[i]:start[i + 1]].copy(), x[start[i]:start[i + 1]].copy())
+            for i in range(n_series.value)]
 
 
 def merge_series(results):

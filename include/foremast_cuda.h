@@ -348,6 +348,20 @@ int32_t fm_synth_fill_device(fm_ctx* ctx, const fm_synth_desc* d, float* d_cur,
 int32_t fm_synth_fill_host(const fm_synth_desc* d, float* cur, float* base,
                            float* hist, uint8_t* metric_type, uint32_t n_threads);
 
+/* Host only (no GPU, no ctx): decode a Prometheus query_range response body -- the step right
+ * before the hot path: the brain fetches the URLs of currentConfig / baselineConfig /
+ * historicalConfig (foremast-service/cmd/manager/main.go:28-74) and gets
+ * {"status":"success","data":{"result":[{"metric":{..},"values":[[ts,"v"],..]},..]}}
+ * (foremast-browser/src/App.js:278-292).  The finite samples of result series i are written to
+ * ts_out / val_out [series_start[i], series_start[i+1]) in the order of the body; NaN / +-Inf
+ * samples (Prometheus gaps) are dropped; values are np.float32(float(v)) bit for bit.
+ * series_start needs cap_series >= number of series + 1 entries.  Returns the number of samples
+ * written, FM_E_INVALID for a malformed body or status != "success", FM_E_NOMEM when a capacity
+ * is too small (text: fm_last_error(NULL)). */
+int64_t fm_decode_query_range(const char* body, uint64_t len, int64_t* ts_out, float* val_out,
+                              uint64_t cap_samples, uint32_t* series_start, uint32_t cap_series,
+                              uint32_t* n_series);
+
 /* Block until all work queued on the ctx stream has finished. */
 int32_t fm_ctx_sync(fm_ctx* ctx);
 

@@ -209,3 +209,54 @@ def test_elasticsearch_store_speaks_the_documents_index():
     assert calls[-1][1] == "http://es:9200/documents/document/a1/_update"
     assert st.update("b2", reason="ok")
     assert docs["b2"]["reason"] == "ok"
+
+
+def _payload(rng, n_series, n_points, style=0):
+    import json
+    res = []
+    t0 = 1554076800
+    for s in range(n_series):
+        vals = []
+        for i in range(n_points):
+            r = rng.random()
+            if r < 0.03:
+                v = rng.choice(["NaN", "+Inf", "-Inf", "Inf"])
+            elif r < 0.2:
+                v = repr(float(rng.integers(0, 50)))
+            elif r < 0.4:
+                v = "%.6e" % rng.normal(0, 1e-5)
+            elif r < 0.45:
+                v = rng.choice(["1e-400", "-0", "0.1", "123456789012345678901234567890", "4.9e-324", "1e400"])
+            else:
+                v = repr(float(rng.normal(100, 30)))
+            ts = t0 + 60 * i if style == 0 else t0 + 60 * i + 0.123
+            vals.append([ts, v])
+        res.append({"metric": {"__name__": 'na"me\\\\{x}', "pod": "p-%d" % s, "nested": "a]b}c"}, "values": vals})
+    body = {"status": "success", "data": {"resultType": "matrix", "result": res}, "warnings": ["x", {"y": [1, 2]}]}
+    return json.dumps(body, indent=None if style == 0 else 1).encode()
+
+
+def test_decode_query_range_fast_equals_python():
+    """C scanner (fm_decode_query_range) against the json.loads decoder: every sample bit for bit,
+    gaps dropped, escapes / nested values in labels skipped, compact and indented bodies."""
+    from foremast_1_b200 import brain
+    rng = np.random.default_rng(3)
+    for style in (0, 1):
+        body = _payload(rng, 7, 300, style)
+        ref = brain.decode_query_range(body)
+        got = brain.decode_query_range_fast(body)
+        assert len(got) == len(ref) == 7
+        for (_, t0, x0), (_, t1, x1) in zip(ref, got):
+            assert np.array_equal(t0, t1)
+            assert x0.tobytes() == x1.tobytes()
+    assert brain.decode_query_range_fast(b'{"status":"success","data":{"resultType":"matrix","result":[]}}') == []
+    one = brain.decode_query_range_fast(b'{"data":{"result":[{"metric":{},"value":[12.5,"3"]}]}}')
+    assert one[0][1].tolist() == [12] and one[0][2].tolist() == [3.0]
+
+
+def test_decode_query_range_fast_errors():
+    from foremast_1_b200 import brain
+    for bad in (b'{"status":"error","errorType":"bad_data","error":"x"}', b'[1,2]', b'{"data":{"result":[{"values":[[1,"2"]',
+                b'{"data":{"result":[{"values":[[1,"abc"]]}]}}', b''):
+        with pytest.raises(ValueError):
+            brain.decode_query_range_fast(bad)
