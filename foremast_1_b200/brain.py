@@ -199,6 +199,15 @@ def decode_query_range_fast(body):
             for i in range(n_series.value)]
 
 
+def decode_response(payload):
+    """What the job loop calls on a fetched body: the C scanner for raw JSON object bodies, the
+    json.loads decoder for everything else (already parsed dicts, the service proxy's
+    double-encoded strings, App.js:281)."""
+    if isinstance(payload, (bytes, bytearray)) and bytes(payload[:64]).lstrip()[:1] == b"{":
+        return decode_query_range_fast(payload)
+    return decode_query_range(payload)
+
+
 def merge_series(results):
     """Several result series of one query (one per pod) -> one time-ordered row,
     the way a single metric alias is judged as one sample set."""
@@ -245,9 +254,9 @@ def score_documents(ctx, docs, fetch=http_fetch, type_names=None, max_hist=10080
             base_cfg = parse_config(doc.get("baselineConfig", "")) if strat in CANARY_STRATEGIES else {}
             hist_cfg = parse_config(doc.get("historicalConfig", ""))
             for alias, url in cur_cfg.items():
-                ts, cur = merge_series(decode_query_range(fetch(url)))
-                base = merge_series(decode_query_range(fetch(base_cfg[alias])))[1] if alias in base_cfg else None
-                hist = merge_series(decode_query_range(fetch(hist_cfg[alias])))[1] if alias in hist_cfg else None
+                ts, cur = merge_series(decode_response(fetch(url)))
+                base = merge_series(decode_response(fetch(base_cfg[alias])))[1] if alias in base_cfg else None
+                hist = merge_series(decode_response(fetch(hist_cfg[alias])))[1] if alias in hist_cfg else None
                 series.append((di, alias, ts, cur, base, hist))
         except Exception as e:  # host I/O problem: the document fails, the batch goes on
             series = [s for s in series if s[0] != di]
