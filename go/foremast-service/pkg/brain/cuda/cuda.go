@@ -19,6 +19,7 @@ package cuda
 import "C"
 
 import (
+	"bytes"
 	"fmt"
 	"runtime"
 	"unsafe"
@@ -187,4 +188,26 @@ func StatusOf(verdicts []uint8) string {
 		return "completed_unknown"
 	}
 	return "completed_health"
+}
+
+// DecodeQueryRange turns a raw Prometheus query_range response body into samples without going
+// through encoding/json: values[i] / ts[i] for i in [start[s], start[s+1]) belong to result
+// series s; NaN and +-Inf samples are dropped (fm_decode_query_range, include/foremast_cuda.h).
+func DecodeQueryRange(body []byte) (ts []int64, values []float32, start []uint32, err error) {
+	if len(body) == 0 {
+		return nil, nil, nil, fmt.Errorf("empty query_range body")
+	}
+	capSamples := len(body)/8 + 1
+	capSeries := bytes.Count(body, []byte(`"value`)) + 2
+	ts = make([]int64, capSamples)
+	values = make([]float32, capSamples)
+	start = make([]uint32, capSeries)
+	var nSeries C.uint32_t
+	n := C.fm_decode_query_range((*C.char)(unsafe.Pointer(&body[0])), C.uint64_t(len(body)),
+		(*C.int64_t)(unsafe.Pointer(&ts[0])), (*C.float)(unsafe.Pointer(&values[0])), C.uint64_t(capSamples),
+		(*C.uint32_t)(unsafe.Pointer(&start[0])), C.uint32_t(capSeries), &nSeries)
+	if n < 0 {
+		return nil, nil, nil, fmt.Errorf("fm_decode_query_range: %d: %s", int64(n), lastError(nil))
+	}
+	return ts[:n], values[:n], start[:int(nSeries)+1], nil
 }
