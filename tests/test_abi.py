@@ -80,3 +80,20 @@ def test_synth_host_is_deterministic_and_typed():
     mem = base[mt == 5].astype(np.float64)
     assert 2e8 < mem.mean() < 2e9 and 1e-4 < (mem.std(axis=1) / mem.mean(axis=1)).mean() < 1e-2
     assert (base[mt == 3] > 0).all() and (base[mt == 4] > 0).all() and (base[mt == 4] < 4.5).all()
+
+
+def test_headline_kernel_does_not_spill():
+    """k_canary_sort<64, 48> sits at the 128-register limit; a build that spills more than a few
+    words costs 10 % and more, so a change that tips it over should be noticed."""
+    import re
+    import shutil
+    import subprocess
+    from foremast_1_b200 import _ffi
+    tool = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(tool):
+        pytest.skip("cuobjdump not available")
+    _ffi.lib()
+    out = subprocess.run([tool, "-res-usage", _ffi.lib_path()], capture_output=True, text=True).stdout
+    m = re.search(r"k_canary_sortILi64ELi48E.*?\n\s*REG:(\d+) STACK:(\d+)", out, re.S)
+    assert m, "kernel not found in the library"
+    assert int(m.group(1)) <= 128 and int(m.group(2)) <= 64, m.groups()
