@@ -3,6 +3,7 @@ include/foremast_cuda.h; the ctypes mirror has the compiled struct sizes."""
 import ctypes as C
 import os
 import re
+import pytest
 
 import numpy as np
 
