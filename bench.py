@@ -97,8 +97,8 @@ def measured_traffic(kernel, workload, n_series):
     (None if this combination was not captured)."""
     try:
         with open(os.path.join(ROOT, "profiles", "r01", "traffic.json")) as f:
-            t = json.load(f).get(kernel)
-        if t is None or t.get("workload") != workload:
+            t = json.load(f).get(kernel, {}).get(workload)
+        if t is None:
             return None
         return int(t["bytes_per_series"]) * int(n_series)
     except Exception:
