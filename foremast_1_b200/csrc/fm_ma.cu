@@ -9,8 +9,8 @@
 // consecutive rows, so a warp's groups read one contiguous span); the history loop is software
 // pipelined with eight 16-byte loads per lane in flight, and the current row is requested first
 // so that its latency hides under the moments.  No shared memory, no staging: nothing is reused.
-// Measured (1M series, 16-byte records, B200): 51 % of the measured HBM copy rate at 60 points,
-// 76 % at 240, 94 % at 480, >100 % from 960 on (profiles/r01/sweep_c5.md).
+// Measured (1M series, 16-byte records, B200): 58 % of the measured HBM copy rate at 60 points,
+// 78 % at 240, 95 % at 480, >100 % from 960 on (profiles/r01/sweep_c5.md).
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -119,6 +119,10 @@ __global__ void __launch_bounds__(256, 4) k_ma_only(const FmKArgs a) {
     uint32_t mlo = 0, mhi = 0;                   // anomaly mask of the (<= 64) current points
     if (model_ok) {
       const bool chk_up = (tp.bound_mask & 1u) != 0, chk_lo = (tp.bound_mask & 2u) != 0;
+      // fp32 x against an fp64 bound, exactly, without converting every x: x > up <=> x > rd(up)
+      // (rd(up) is the largest float <= up, so the next float above it exceeds up), and
+      // x < lo <=> x < ru(lo); NaN bounds compare false either way.
+      const float up_f = __double2float_rd(up), lo_f = __double2float_ru(lo);
 #pragma unroll
       for (int j = 0; j < CV; ++j) {
         const uint32_t v = gl + j * G;
@@ -126,8 +130,7 @@ __global__ void __launch_bounds__(256, 4) k_ma_only(const FmKArgs a) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const uint32_t p = 4u * v + k;
-          const double xd = (double)x[k];
-          const bool f = p < nc && ((chk_up && xd > up) || (chk_lo && xd < lo));
+          const bool f = p < nc && ((chk_up && x[k] > up_f) || (chk_lo && x[k] < lo_f));
           if (f) { if (p < 32u) mlo |= 1u << p; else mhi |= 1u << (p - 32u); }
         }
       }
