@@ -12,13 +12,19 @@ libforemast_cuda.so through engine.Context.
   params_from_env       the env block of deploy/foremast/3_brain/foremast-brain.yaml:21-81
   decode_query_range    Prometheus query_range JSON -> (timestamps, values) rows
                         (response shape: foremast-browser/src/App.js:278-292)
+  merge_series          the samples of one query on the 60 s grid the reference queries on
+                        (foremast-barrelman/pkg/client/metrics/metricsquery.go:43-78), one row per alias
+  parse_go_time /       Document time fields as Go's time.Time marshals them (RFC3339, nanoseconds;
+  format_go_time        foremast-service/pkg/models/models.go:86-89)
   score_documents       one poll of "initial" documents -> one coalesced batch ->
                         status / reason / anomalyInfo per document
   BrainWorker           poll / claim / takeover loop over a document store
                         (pkg/search/elasticsearchstore.go:124-149; design.md:37-43)
 """
+import calendar
 import ctypes as C
 import json
+import re
 import time
 import urllib.request
 
@@ -59,6 +65,53 @@ def external_status(status):
     if status in (ST_UNKNOWN, ST_PRE_FAILED, ST_ABORT):
         return "abort"
     return "inprogress"
+
+
+# Document.CreatedAt / StartTime / EndTime / ModifiedAt are time.Time (models.go:86-89): in the
+# 'documents' index they are RFC3339 strings with up to nine fractional digits, "Z" for UTC
+# (CreateNewDoc writes time.Now().UTC(), elasticsearchstore.go:42-45) or a numeric offset
+# (StartTime / EndTime are parsed from the request, common/timeutils.go:9-19).
+_GO_TIME = re.compile(r"^(\d{4})-(\d\d)-(\d\d)[Tt ](\d\d):(\d\d):(\d\d)(?:[.,](\d{1,9}))?([Zz]|[+-]\d\d:?\d\d)$")
+
+
+def parse_go_time(v):
+    """RFC3339 string -> unix seconds (float); None for empty values and Go's zero time
+    (0001-01-01T00:00:00Z, what an unset time.Time marshals to).  Numbers pass through, so that
+    documents written by older workers of this package are still understood."""
+    if v is None or v == "":
+        return None
+    if isinstance(v, (int, float)):
+        return float(v)
+    m = _GO_TIME.match(str(v).strip())
+    if not m:
+        raise ValueError(f"not an RFC3339 time: {v!r}")
+    y, mo, d, hh, mi, ss = (int(m.group(i)) for i in range(1, 7))
+    if y <= 1:
+        return None
+    t = calendar.timegm((y, mo, d, hh, mi, ss, 0, 0, 0))
+    if m.group(7):
+        t += int(m.group(7).ljust(9, "0")) / 1e9
+    z = m.group(8)
+    if z not in "Zz":
+        sign = -1 if z[0] == "-" else 1
+        digits = z[1:].replace(":", "")
+        t -= sign * (int(digits[:2]) * 3600 + int(digits[2:]) * 60)
+    return float(t)
+
+
+def format_go_time(t):
+    """unix seconds -> what json.Marshal(time.Time in UTC) writes: RFC3339 with the fractional
+    part trimmed of trailing zeros and left out when it is zero (Go's RFC3339Nano layout)."""
+    t = float(t)
+    sec = int(t // 1)
+    frac = int(round((t - sec) * 1e6)) * 1000          # a float clock resolves microseconds at best
+    if frac >= 1_000_000_000:
+        sec, frac = sec + 1, 0
+    st = time.gmtime(sec)
+    out = "%04d-%02d-%02dT%02d:%02d:%02d" % (st.tm_year, st.tm_mon, st.tm_mday, st.tm_hour, st.tm_min, st.tm_sec)
+    if frac:
+        out += "." + ("%09d" % frac).rstrip("0")
+    return out + "Z"
 
 
 def parse_config(s):
@@ -208,15 +261,47 @@ def decode_response(payload):
     return decode_query_range(payload)
 
 
-def merge_series(results):
-    """Several result series of one query (one per pod) -> one time-ordered row,
-    the way a single metric alias is judged as one sample set."""
-    if not results:
+STEP_SECONDS = 60        # metricsquery.go:43: every query is made with step 60 on a step-aligned range
+
+
+def align_to_grid(ts, x, step=STEP_SECONDS):
+    """Samples of ONE result series -> (grid index int64[], value float32[]), ascending, one sample
+    per grid slot.  The reference asks Prometheus for start/end that are multiples of the step
+    (metricsquery.go:43-46, 52-78), so samples sit on the grid already; anything else (a proxy that
+    shifts timestamps, a sub-step scrape) is snapped to the nearest slot and the last sample of a
+    slot wins.  Gaps stay gaps: the rows handed to the library are compacted, never interpolated."""
+    if ts.size == 0:
         return np.zeros(0, np.int64), np.zeros(0, np.float32)
-    ts = np.concatenate([r[1] for r in results])
-    x = np.concatenate([r[2] for r in results])
-    o = np.argsort(ts, kind="stable")
-    return ts[o], x[o]
+    g = (ts.astype(np.int64) + step // 2) // step
+    o = np.argsort(g, kind="stable")
+    g, x = g[o], x[o]
+    last = np.ones(g.size, bool)
+    last[:-1] = g[1:] != g[:-1]
+    return g[last], x[last]
+
+
+def merge_series(results, step=STEP_SECONDS):
+    """All result series of one query -> ONE row per metric alias on the step grid.
+
+    Declared rule: a query that matches several pods
+    (`namespace_pod:...{pod=~"a|b"}`, metricsquery.go:52-64) is judged as one sample set whose value
+    at a grid point is the MEAN over the pods that reported there — the same aggregation the
+    `namespace_app_per_pod:*` recording rules apply to the historical series the bounds come from
+    (deploy/foremast/2_barrelman/metrics-rules-default.yaml:12-84), so current, baseline and
+    history stay comparable.  Grid points where no pod reported are dropped (gap compaction).
+    Returns (timestamps int64[] = grid index * step, values float32[])."""
+    rows = [align_to_grid(r[1], r[2], step) for r in results]
+    rows = [r for r in rows if r[0].size]
+    if not rows:
+        return np.zeros(0, np.int64), np.zeros(0, np.float32)
+    if len(rows) == 1:
+        return rows[0][0] * step, rows[0][1]
+    g = np.concatenate([r[0] for r in rows])
+    x = np.concatenate([r[1] for r in rows]).astype(np.float64)
+    ug, inv = np.unique(g, return_inverse=True)
+    tot = np.bincount(inv, weights=x, minlength=ug.size)
+    cnt = np.bincount(inv, minlength=ug.size)
+    return ug * step, (tot / cnt).astype(np.float32)
 
 
 def http_fetch(url, timeout=30):
@@ -224,8 +309,13 @@ def http_fetch(url, timeout=30):
         return r.read()
 
 
-def _rows(mats, width):
-    m = np.zeros((len(mats), max(4, A.row_pitch(width))), np.float32)
+def _rows(ctx, role, mats, width):
+    """Ragged rows -> (matrix [S x pitch] fp32, lens uint32).  With a real engine.Context the matrix
+    is a view of PINNED host memory owned by the ctx (fm_alloc_pinned, reused from poll to poll), so
+    fm_score_batch copies straight out of it; the stand-in contexts of the CPU tests get numpy."""
+    shape = (len(mats), max(4, A.row_pitch(width)))
+    alloc = getattr(ctx, "pinned_rows", None)
+    m = alloc(role, shape) if alloc else np.zeros(shape, np.float32)
     lens = np.zeros(len(mats), np.uint32)
     for i, x in enumerate(mats):
         n = min(x.size, width)
@@ -234,17 +324,17 @@ def _rows(mats, width):
     return m, lens
 
 
-def score_documents(ctx, docs, fetch=http_fetch, type_names=None, max_hist=10080, max_base=None):
-    """Score every metric of every document in ONE coalesced batch.
+def _failed(reason):
+    return {"status": ST_PRE_FAILED, "reason": reason, "anomalyInfo": "", "processingContent": "", "metrics": {},
+            "gauges": []}
 
-    docs: dicts with the Document fields (id, currentConfig, baselineConfig,
-    historicalConfig, strategy).  Returns {id: {"status", "reason", "anomalyInfo",
-    "processingContent", "metrics"}}.  A document whose configs cannot be parsed
-    or fetched gets "preprocess_failed" with the reason; scoring the others goes on.
-    """
-    type_names = type_names or dict(A.METRIC_TYPES)
-    series = []       # (doc idx, alias, ts_cur, cur, base, hist)
-    results = {}
+
+def fetch_documents(docs, fetch=http_fetch):
+    """Preprocessing (the state diagram's preprocess_* half): parse the three config strings of every
+    document, fetch and decode the series.  Returns (series, failed): series = list of
+    (doc index, alias, ts_cur, cur, base, hist); failed = {doc id: result} for documents whose configs
+    cannot be parsed or fetched ("preprocess_failed" with the reason; the others go on)."""
+    series, failed = [], {}
     for di, doc in enumerate(docs):
         try:
             cur_cfg = parse_config(doc.get("currentConfig", ""))
@@ -252,39 +342,50 @@ def score_documents(ctx, docs, fetch=http_fetch, type_names=None, max_hist=10080
                 raise ValueError("currentConfig is empty")
             strat = (doc.get("strategy") or "").lower()
             base_cfg = parse_config(doc.get("baselineConfig", "")) if strat in CANARY_STRATEGIES else {}
-            hist_cfg = parse_config(doc.get("historicalConfig", ""))
+            # Document says historicalConfig, DocumentResponse historicConfig (models.go:92,130)
+            hist_cfg = parse_config(doc.get("historicalConfig") or doc.get("historicConfig") or "")
+            mine = []
             for alias, url in cur_cfg.items():
                 ts, cur = merge_series(decode_response(fetch(url)))
                 base = merge_series(decode_response(fetch(base_cfg[alias])))[1] if alias in base_cfg else None
                 hist = merge_series(decode_response(fetch(hist_cfg[alias])))[1] if alias in hist_cfg else None
-                series.append((di, alias, ts, cur, base, hist))
+                mine.append((di, alias, ts, cur, base, hist))
+            series += mine
         except Exception as e:  # host I/O problem: the document fails, the batch goes on
-            series = [s for s in series if s[0] != di]
-            results[doc["id"]] = {"status": ST_PRE_FAILED, "reason": f"{type(e).__name__}: {e}",
-                                  "anomalyInfo": "", "processingContent": "", "metrics": {}}
+            failed[doc["id"]] = _failed(f"{type(e).__name__}: {e}")
+    return series, failed
+
+
+def score_series(ctx, docs, series, failed=None, type_names=None, max_hist=10080, max_base=None):
+    """Postprocessing: every fetched metric of every document in ONE coalesced batch per strategy
+    kind, then per document the A.9 roll-up over its metrics, reason and anomalyInfo."""
+    type_names = type_names or dict(A.METRIC_TYPES)
+    results = dict(failed or {})
     out = {}
     # canary series (with a baseline) and historical-only series are two batches
     for canary in (True, False):
         idx = [i for i, s in enumerate(series) if (s[4] is not None) == canary]
         if not idx:
             continue
+        tag = "c" if canary else "h"
         cur_w = max(1, max(series[i][3].size for i in idx))
         if cur_w > A.FM_MAX_CUR:
             cur_w = A.FM_MAX_CUR
-        cur, cl = _rows([series[i][3] for i in idx], cur_w)
+        cur, cl = _rows(ctx, tag + "cur", [series[i][3] for i in idx], cur_w)
         hist = hl = base = bl = None
         if any(series[i][5] is not None for i in idx):
             hw = min(max_hist, max(1, max((series[i][5].size if series[i][5] is not None else 0) for i in idx)))
-            hist, hl = _rows([series[i][5] if series[i][5] is not None else np.zeros(0, np.float32) for i in idx], hw)
+            hist, hl = _rows(ctx, tag + "hist",
+                             [series[i][5] if series[i][5] is not None else np.zeros(0, np.float32) for i in idx], hw)
         if canary:
             bw = max(1, max(series[i][4].size for i in idx))
             bw = min(bw, max_base or (A.FM_MAX_RANK_N - cur_w))
-            base, bl = _rows([series[i][4] for i in idx], bw)
+            base, bl = _rows(ctx, tag + "base", [series[i][4] for i in idx], bw)
         mt = np.array([metric_type_id(series[i][1], type_names) for i in idx], np.uint8)
         r = ctx.score(cur, base, hist, strategy=A.FM_STRAT_CANARY if canary else A.FM_STRAT_HISTORICAL,
                       cur_len=cl, base_len=bl, hist_len=hl, metric_type=mt)
         for j, i in enumerate(idx):
-            out[i] = r["rec"][j]
+            out[i] = r["rec"][j].copy()
     # per document: A.9 roll-up over its metrics, reason, anomalyInfo (models.go:60-63;
     # values are [t0, v0, t1, v1, ...] as decoded by Barrelman.go:593-620)
     for di, doc in enumerate(docs):
@@ -300,29 +401,41 @@ def score_documents(ctx, docs, fetch=http_fetch, type_names=None, max_hist=10080
             verdict = A.FM_UNKNOWN
         else:
             verdict = A.FM_HEALTHY
-        anomaly, reasons, metrics = {}, [], {}
+        anomaly, reasons, metrics, gauge_rows = {}, [], {}, []
         for i, (_, alias, ts, cur, _b, _h) in mine:
             rec = out[i]
             metrics[alias] = {k: (float(rec[k]) if rec[k].dtype.kind == "f" else int(rec[k])) for k in rec.dtype.names}
+            anom_ts = []
             if rec["verdict"] == A.FM_UNHEALTHY:
                 n = min(cur.size, A.FM_MAX_CUR)
                 off = cur.size - n
                 x = cur[off:].astype(np.float64)
-                bm = int(ctx.table[metric_type_id(alias, type_names) if metric_type_id(alias, type_names) < len(ctx.table) else 0].bound_mask)
+                tid = metric_type_id(alias, type_names)
+                bm = int(ctx.table[tid if tid < len(ctx.table) else 0].bound_mask)
                 flag = ((bm & 1) != 0) & (x > rec["upper"]) | ((bm & 2) != 0) & (x < rec["lower"])
                 vals = []
                 for k in np.nonzero(flag)[0]:
                     vals += [int(ts[off + k]), float(x[k])]
+                    anom_ts.append(int(ts[off + k]))
                 anomaly[alias] = {"tags": "", "values": vals}
                 reasons.append(f"{alias}: {int(rec['n_anom'])} anomalous point(s) outside "
                                f"[{rec['lower']:.6g}, {rec['upper']:.6g}]")
             elif rec["verdict"] == A.FM_UNKNOWN:
                 reasons.append(f"{alias}: " + ("no current metric" if rec["status"] & A.FM_ST_NO_CURRENT
                                                else "not enough historical data"))
+            if not (rec["status"] & A.FM_ST_HIST_INSUFFICIENT):
+                gauge_rows.append((alias, rec, {"app": doc.get("appName", "")} if doc.get("appName") else {}, anom_ts))
         results[doc["id"]] = {"status": VERDICT_STATUS[verdict], "reason": "; ".join(reasons),
                               "anomalyInfo": json.dumps(anomaly) if anomaly else "",
-                              "processingContent": "", "metrics": metrics}
+                              "processingContent": "", "metrics": metrics, "gauges": gauge_rows}
     return results
+
+
+def score_documents(ctx, docs, fetch=http_fetch, type_names=None, max_hist=10080, max_base=None):
+    """fetch_documents + score_series: one poll of documents -> {id: {"status", "reason",
+    "anomalyInfo", "processingContent", "metrics", "gauges"}}."""
+    series, failed = fetch_documents(docs, fetch)
+    return score_series(ctx, docs, series, failed, type_names, max_hist, max_base)
 
 
 class MemoryStore:
@@ -352,6 +465,8 @@ class ElasticsearchStore:
     update      POST /documents/document/<id>/_update with a script that applies the fields only
                 while modified_at still has the value the caller saw (the claim / takeover race
                 between brain workers); Elasticsearch answers "noop" when somebody else won.
+                modified_at travels as the RFC3339 string the service wrote / this worker writes,
+                and is compared as that string.
 
     `transport(method, url, body_dict) -> dict` defaults to urllib; tests inject a fake."""
 
@@ -390,34 +505,69 @@ class ElasticsearchStore:
 
 
 class BrainWorker:
-    """Poll / claim / score / write-back loop (design.md:37-43).
+    """Poll / claim / score / write-back loop (design.md:37-43; state diagram
+    .gitbook/assets/foremastrequeststatediagram.png; status names converter.go:13-26).
 
-    - claims "initial" documents by moving them to preprocess_inprogress with a
-      modified_at stamp; a document stuck in an *_inprogress state for longer
-      than MAX_STUCK_IN_SECONDS (foremast-brain.yaml:80-81) is taken over;
-    - fail fast: unhealthy completes the job at once; a healthy verdict before
-      endTime puts the job back to "initial" so it is re-judged on the next poll
-      ("continuous to monitor ... until endTime is reached", design.md:43);
-    - all claimed documents of one poll are scored as one batch.
+      initial --claim--> preprocess_inprogress --fetched--> preprocess_completed
+              --> postprocess_inprogress --scored--> completed_health | completed_unhealth |
+              completed_unknown        (fetch problems: preprocess_failed)
+
+    - every transition is an optimistic update on `modified_at`: the stamp this worker wrote last
+      must still be there, else another worker has taken the job over and this one drops it.
+      Stamps are RFC3339 UTC strings, the way the service's time.Time fields are stored
+      (models.go:86-89); times are never written as numbers;
+    - a document that sits in an *_inprogress / preprocess_completed state for longer than
+      MAX_STUCK_IN_SECONDS (foremast-brain.yaml:80-81) is taken over;
+    - fail fast: unhealthy completes the job at once; a healthy verdict before endTime puts the job
+      back to "initial" so it is re-judged on the next poll ("continuous to monitor ... until
+      endTime is reached", design.md:43);
+    - all claimed documents of one poll are scored as one batch; a document whose write-back fails
+      does not stop the others;
+    - `gauges` (a gauges.GaugeRegistry, optional) receives the bounds and anomaly points of every
+      scored metric: what :8000/metrics serves (foremast-brain.yaml:87-122).
     """
 
-    def __init__(self, ctx, store, fetch=http_fetch, env=None, now=time.time):
-        self.ctx, self.store, self.fetch, self.now = ctx, store, fetch, now
+    IN_FLIGHT = (ST_PRE_INPROGRESS, ST_PRE_COMPLETED, ST_POST_INPROGRESS)
+
+    def __init__(self, ctx, store, fetch=http_fetch, env=None, now=time.time, gauges=None):
+        self.ctx, self.store, self.fetch, self.now, self.gauges = ctx, store, fetch, now, gauges
         env = env or {}
         self.max_stuck = float(env.get("MAX_STUCK_IN_SECONDS", "90"))
         g, table, names = params_from_env(env)
         self.type_names = names
         ctx.set_params(g, table)
+        self.errors = []          # (doc id, message) of write-backs that failed
+
+    def _stamp(self):
+        return format_go_time(self.now())
+
+    def _move(self, d, status, **fields):
+        """One optimistic transition; d carries the stamp it was last seen / written with."""
+        stamp = self._stamp()
+        if stamp == d.get("modified_at"):        # two transitions inside one clock tick: stay distinguishable
+            stamp = format_go_time(parse_go_time(stamp) + 1e-6)
+        try:
+            ok = self.store.update(d["id"], expect_modified_at=d.get("modified_at"), status=status,
+                                   modified_at=stamp, **fields)
+        except Exception as e:                    # store trouble on one document does not strand the batch
+            self.errors.append((d["id"], f"{type(e).__name__}: {e}"))
+            return False
+        if ok:
+            d["status"], d["modified_at"] = status, stamp
+        return ok
 
     def claim(self):
         now = self.now()
         claimed = []
-        for d in self.store.by_status({ST_INITIAL, ST_PRE_INPROGRESS, ST_POST_INPROGRESS}):
-            if d["status"] != ST_INITIAL and now - float(d.get("modified_at", 0)) <= self.max_stuck:
-                continue                                   # another worker is on it
-            if self.store.update(d["id"], expect_modified_at=d.get("modified_at"),
-                                 status=ST_PRE_INPROGRESS, modified_at=now):
-                d["status"], d["modified_at"] = ST_PRE_INPROGRESS, now
+        for d in self.store.by_status({ST_INITIAL, *self.IN_FLIGHT}):
+            if d["status"] != ST_INITIAL:
+                try:
+                    seen = parse_go_time(d.get("modified_at"))
+                except ValueError:
+                    seen = None
+                if seen is not None and now - seen <= self.max_stuck:
+                    continue                               # another worker is on it
+            if self._move(d, ST_PRE_INPROGRESS):
                 claimed.append(d)
         return claimed
 
@@ -425,15 +575,35 @@ class BrainWorker:
         docs = self.claim()
         if not docs:
             return {}
-        res = score_documents(self.ctx, docs, self.fetch, self.type_names)
-        now = self.now()
+        series, failed = fetch_documents(docs, self.fetch)
+        live = []
         for d in docs:
+            if d["id"] in failed:
+                r = failed[d["id"]]
+                self._move(d, ST_PRE_FAILED, reason=r["reason"])
+                r["written_status"] = d["status"]
+            elif self._move(d, ST_PRE_COMPLETED) and self._move(d, ST_POST_INPROGRESS):
+                live.append(d)
+        keep = {id(d) for d in live}
+        index = {i: j for j, i in enumerate(i for i, d in enumerate(docs) if id(d) in keep)}
+        series = [(index[s[0]],) + tuple(s[1:]) for s in series if s[0] in index]
+        res = score_series(self.ctx, live, series, None, self.type_names)
+        now = self.now()
+        for d in live:
             r = res[d["id"]]
             status = r["status"]
-            end = d.get("endTime")
-            if status == ST_HEALTH and end is not None and now < float(end):
+            try:
+                end = parse_go_time(d.get("endTime"))
+            except ValueError:
+                end = None
+            if status == ST_HEALTH and end is not None and now < end:
                 status = ST_INITIAL                       # keep watching until endTime
-            self.store.update(d["id"], status=status, reason=r["reason"], anomalyInfo=r["anomalyInfo"],
-                              modified_at=now)
-            r["written_status"] = status
+            # the claim stamp must still be ours: a worker that took the job over meanwhile wins
+            if self._move(d, status, reason=r["reason"], anomalyInfo=r["anomalyInfo"]):
+                r["written_status"] = status
+                if self.gauges is not None:
+                    self.gauges.update(d["id"], r["gauges"], final=status != ST_INITIAL)
+            else:
+                r["written_status"] = None
+        res.update(failed)
         return res

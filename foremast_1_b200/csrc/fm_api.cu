@@ -48,10 +48,16 @@ struct fm_ctx {
   Arena in[2], out[2], roll, misc;
   cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
   std::vector<cudaEvent_t> kev;    // per-chunk kernel timing events
-  int score_smem_set = 0, groups_smem_set = 0, sort_smem_set = 0, elect_smem_set = 0;
+  int score_smem_set = 0, groups_smem_set = 0, sort_smem_set = 0, elect_smem_set = 0, count_smem_set = 0;
+  // Diagnostic switches, read ONCE when the ctx is created (none is needed in production):
   int force_path = 0;              // FOREMAST_CUDA_PATH: generic = 1 (shared-memory sort kernel only),
-                                   // elect = 3 (election-multiset canary kernel), else 0 = auto
-  int force_stages = 0;            // FOREMAST_CUDA_STAGES=1|2: staging buffers per warp of the fast path
+                                   // sort = 2 (register-sort canary kernel), elect = 3 (CTA-per-series
+                                   // election kernel), else 0 = auto (counting kernel where it applies)
+  int force_stages = 0;            // FOREMAST_CUDA_STAGES=1|2: staging buffers per warp of the elect path
+  int count_slots = 0;             // FOREMAST_CUDA_SLOTS: election-table slots of the counting kernel
+  int count_warps = 0;             // FOREMAST_CUDA_WARPS: warps per SM of the counting kernel
+  int ma_group = 0;                // FOREMAST_CUDA_MA_GROUP=4|8|16|32: lanes per series of k_ma_only
+  int small_table = 0;             // FOREMAST_CUDA_SMALL_TABLE: elect path, load factor <= 0.8
   std::string err;
 };
 
@@ -88,7 +94,8 @@ uint32_t round4(uint32_t n) { return (n + 3u) & ~3u; }
 
 bool mode_has(uint32_t mode, uint32_t t) { return mode == t || mode == FM_PW_ALL || mode == FM_PW_ANY; }
 
-// kind: 0 = k_score_series (generic), 2 = k_canary_sort<regs>, 3 = k_canary_elect<regs>, 4 = k_ma_only<regs>
+// kind: 0 = k_score_series (generic), 2 = k_canary_sort<regs>, 3 = k_canary_elect<regs>, 4 = k_ma_only<regs>,
+// 5 = k_canary_count<regs, valid>
 struct Plan { FmKArgs a; int wpc; int grid; bool fast; int kind; int regs; int valid; };
 
 void fill_common(fm_ctx* c, const fm_batch* b, bool canary, FmKArgs& a) {
@@ -112,7 +119,7 @@ int32_t plan_canary_elect(fm_ctx* c, const fm_batch* b, Plan* pl) {
   a.base_cap = round4(b->n_base);
   a.log_m = 8;
   while ((1u << a.log_m) < (b->n_cur + b->n_base) * 5u / 2u) ++a.log_m;
-  if (getenv("FOREMAST_CUDA_SMALL_TABLE") && a.log_m > 8) --a.log_m;   // experiment: load factor <= 0.8
+  if (c->small_table && a.log_m > 8) --a.log_m;   // experiment: load factor <= 0.8
   const int nv = std::max(1, (int)((((b->n_base + 3u) >> 2) + 127u) / 128u));
   auto bytes = [&](uint32_t stages) {
     size_t x = fm_canary_elect_fixed_bytes() + (size_t)stages * (64 + a.base_cap) * 4 +
@@ -175,12 +182,52 @@ int32_t plan_canary_sort(fm_ctx* c, const fm_batch* b, Plan* pl) {
   return FM_OK;
 }
 
+// k_canary_count<NV, NS> (fm_canary_count.cu): current row <= 63 points, baseline <= 2048 points; the
+// baseline is not sorted (U by searching every baseline point in the sorted current row, T from an
+// election hash multiset).  Per warp: mbarrier, one staging buffer (rows, then the overflow lists),
+// the search tables of the current row and the election table {pattern, counter} x slots.
+int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
+  FmKArgs& a = pl->a;
+  int nv = 0, ns = 0;
+  const uint32_t cap = fm_canary_count_tier(b->n_base, &nv, &ns);
+  if (!cap) return fail(c, FM_E_UNSUPPORTED, "baseline too long for the counting path");
+  a.cur_cap = 64;
+  a.base_cap = cap;
+  a.n_stages = 1;
+  // slots: ~0.7 per key keeps the first round's losers near 45 % at 15 warps per SM (measured
+  // trade-off between overflow rounds and resident warps: DESIGN.md section 5)
+  uint32_t slots = c->count_slots ? (uint32_t)c->count_slots : std::max(64u, ((b->n_cur + cap) * 11u / 16u));
+  slots = (slots + 3u) & ~3u;
+  a.log_m = slots;
+  a.warp_bytes = (uint32_t)((fm_canary_count_fixed_bytes() + (size_t)(64 + cap) * 4 + (size_t)slots * 8 + 127) & ~size_t(127));
+  const size_t limit = c->smem_optin ? c->smem_optin : 232448;
+  const size_t sm_total = 233472;
+  const int max_warps = c->count_warps ? c->count_warps : 16;     // 128 registers per thread
+  int best_w = 1, best_total = 0;
+  for (int w = 1; w <= 8; ++w) {
+    const size_t cta = (size_t)w * a.warp_bytes;
+    if (cta > limit) break;
+    int ctas = (int)(sm_total / (cta + 1024));
+    ctas = std::min(ctas, max_warps / w);
+    if (ctas < 1) continue;
+    if (ctas * w >= best_total) { best_total = ctas * w; best_w = w; }
+  }
+  if (best_total == 0) return fail(c, FM_E_UNSUPPORTED, "canary counting path does not fit shared memory");
+  pl->wpc = best_w;
+  const uint64_t need = (b->n_series + best_w - 1) / best_w;
+  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * (best_total / best_w), need));
+  if (!c->count_smem_set) { FM_CK(c, fm_canary_count_smem_attr((int)limit)); c->count_smem_set = 1; }
+  fill_common(c, b, true, a);
+  pl->fast = true; pl->kind = 5; pl->regs = nv; pl->valid = ns;
+  return FM_OK;
+}
+
 // k_ma_only<G> (fm_ma.cu): no baseline, plain moving_average_all model, current row <= 64 points.
 int32_t plan_ma_only(fm_ctx* c, const fm_batch* b, Plan* pl) {
   FmKArgs& a = pl->a;
   fill_common(c, b, false, a);
   pl->regs = b->n_hist >= 1200 ? 16 : (b->n_hist >= 200 ? 8 : 4);      // lanes per series (profiles/r01/sweep_c5.md)
-  if (const char* e = getenv("FOREMAST_CUDA_MA_GROUP")) pl->regs = atoi(e);   // experiment
+  if (c->ma_group) pl->regs = c->ma_group;   // experiment
   const uint64_t per_warp = 32 / pl->regs;
   const uint64_t need = (b->n_series + per_warp * 8 - 1) / (per_warp * 8);   // 8 warps per CTA
   pl->wpc = 8;
@@ -202,6 +249,7 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
     return plan_ma_only(c, b, pl);
   if (canary && c->force_path != 1 && b->n_cur <= 64 && b->n_base >= 1) {
     if (c->force_path == 3 && b->n_base <= 2048) return plan_canary_elect(c, b, pl);
+    if (c->force_path != 2 && b->n_cur <= 63 && b->n_base <= 2048) return plan_canary_count(c, b, pl);
     if (b->n_base <= 2048) return plan_canary_sort(c, b, pl);
   }
   a.cur_cap = std::max(4u, round4(b->n_cur));
@@ -251,6 +299,7 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
 }
 
 int launch_plan(const Plan& pl, cudaStream_t st) {
+  if (pl.kind == 5) return fm_launch_canary_count(pl.a, pl.regs, pl.valid, pl.wpc, pl.grid, st);
   if (pl.kind == 4) return fm_launch_ma_only(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 3) return fm_launch_canary_elect(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 2) return fm_launch_canary_sort(pl.a, pl.regs, pl.valid, pl.wpc, pl.grid, st);
@@ -355,8 +404,12 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
   c->num_sms = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
   if (const char* e = getenv("FOREMAST_CUDA_PATH"))
-    c->force_path = strcmp(e, "generic") == 0 ? 1 : (strcmp(e, "elect") == 0 ? 3 : 0);
+    c->force_path = strcmp(e, "generic") == 0 ? 1 : (strcmp(e, "sort") == 0 ? 2 : (strcmp(e, "elect") == 0 ? 3 : 0));
   if (const char* e = getenv("FOREMAST_CUDA_STAGES")) c->force_stages = (e[0] == '1') ? 1 : (e[0] == '2' ? 2 : 0);
+  if (const char* e = getenv("FOREMAST_CUDA_SLOTS")) { const int v = atoi(e); c->count_slots = (v >= 64 && v <= 8192) ? v : 0; }
+  if (const char* e = getenv("FOREMAST_CUDA_WARPS")) { const int v = atoi(e); c->count_warps = (v >= 1 && v <= 32) ? v : 0; }
+  if (const char* e = getenv("FOREMAST_CUDA_MA_GROUP")) { const int v = atoi(e); c->ma_group = (v == 4 || v == 8 || v == 16 || v == 32) ? v : 0; }
+  c->small_table = getenv("FOREMAST_CUDA_SMALL_TABLE") != nullptr;
   FM_CKC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   FM_CKC(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
   FM_CKC(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));

@@ -1,0 +1,578 @@
+// fm_canary_count.cu — canary hot path WITHOUT sorting the baseline (BASELINE.json configs[0..2]).
+//
+// One warp per series, persistent over the batch, rows staged by the TMA unit (cp.async.bulk +
+// mbarrier) exactly as in fm_canary_sort.cu.  What differs is the rank stage:
+//
+//   2*R1  Only the <= 63 current points are sorted (two keys per lane, warp network).  Every
+//         baseline point b, held in a register, is located in that sorted row by a branch-free
+//         binary search in shared memory (5 probes after a first comparison against the middle
+//         key, which every lane holds in a register), giving lbc(b) = #{c < b} and, from a
+//         run-length stored beside the key it lands on, ubc(b) = #{c <= b}:
+//             2*R1 = n1(n1+1) + 2 n1 n2 - sum_b (lbc(b) + ubc(b)).
+//   T     The tie term needs the multiset of all n1 + n2 values, not their order.  It is built by
+//         ELECTION in a shared-memory table: pass A, every key stores its bit pattern at
+//         slot hash(key) (plain store, somebody wins); pass B, every key reads the slot back: my
+//         own pattern there -> my class owns the slot, a returned atomic increment of the slot's
+//         counter is my arrival number p and T += 3p(p+1) (sum_{p<t} 3p(p+1) = t^3 - t);
+//         another pattern -> my whole class lost (equal values hash equally) and the key goes to
+//         an overflow list, which is replayed with another hash multiplier until it is empty.
+//         Classes move together, so each is counted exactly once.  Register slots that hold no
+//         sample carry one NaN pattern; the class they form is subtracted at the end.
+//   W     Wilcoxon as before (64 fp64 |differences| sorted across the warp), tie runs read off two
+//         ballots instead of warp scans.
+//   a5..  ONE fp64 division, ONE square root and ONE erfc per series: lanes 0..4 each bring their
+//         statistic into the form num * sqrt(Q / P) (Mann-Whitney, Wilcoxon, Kruskal, sigma, mean)
+//         and evaluate it side by side.
+//
+// The integers (2*R1, T, W+, W-) are bit-identical to the sorting kernels and to the oracle; the
+// fp64 results agree to rounding (1e-15), far inside the 1e-6 contract.
+#include <cstdint>
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include "fm_canary_common.cuh"
+
+namespace {
+using namespace fmc;
+
+constexpr uint32_t kNoKey = 0x7FC00001u;      // NaN pattern of register slots that hold no sample
+constexpr uint32_t kSearchBytes = 272;        // 65 floats (one pad word between the halves) + pad
+constexpr uint32_t kFinalBytes = 528;         // 65 x {key, run length << 16 | 2 * position} + pad
+constexpr uint32_t kMaxRounds = 16;
+
+__device__ __forceinline__ uint2 lds_v2(uint32_t a) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_v2(uint32_t a, uint32_t x, uint32_t y) {
+  asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(a), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void sts_zero16(uint32_t a) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(a), "r"(0u) : "memory");
+}
+__device__ __forceinline__ uint32_t mult_of(uint32_t round) {
+  return (0x9E3779B1u + round * 0x7F4A7C15u) | 1u;          // a different odd multiplier per round
+}
+__device__ __forceinline__ uint32_t slot_of(uint32_t bits, uint32_t mult, uint32_t m) {
+  return __umulhi(bits * mult, m) << 2;                       // byte offset into a table of m slots
+}
+
+// Runs of a sorted 64-key sequence held as positions lane (a) and lane + 32 (b), from the ballots
+// of "my key differs from the previous position's": start of my run (lo) and first position
+// after it (e).  Bit 0 of ba is always set.
+__device__ __forceinline__ void runs_from_ballots(uint32_t ba, uint32_t bb, int lane, uint32_t& lo_a,
+                                                  uint32_t& e_a, uint32_t& lo_b, uint32_t& e_b) {
+  const uint32_t le = (2u << lane) - 1u;                      // bits <= lane
+  const uint32_t up_a = ba & ~le, up_b = bb & ~le, dn_b = bb & le;
+  lo_a = 31u - (uint32_t)__clz((int)(ba & le));
+  e_a = up_a ? (uint32_t)__ffs((int)up_a) - 1u : (bb ? 31u + (uint32_t)__ffs((int)bb) : 64u);
+  lo_b = dn_b ? 63u - (uint32_t)__clz((int)dn_b) : 31u - (uint32_t)__clz((int)ba);
+  e_b = up_b ? 31u + (uint32_t)__ffs((int)up_b) : 64u;
+}
+
+// Wilcoxon signed rank, integers only: n' = non-zero pairs, 2W+, 2W-, tie term.
+struct WxInts { uint32_t np, wp2, wm2, t; bool run; };
+__device__ __forceinline__ WxInts wilcoxon_ints(const fm_global_params& g, WxKeys k, int lane) {
+  WxInts r = {0u, 0u, 0u, 0u, false};
+  r.np = k.n_pairs - __reduce_add_sync(FM_FULL, k.nz);
+  if (!(r.np >= g.min_wx && r.np > 0)) return r;
+  r.run = true;
+  unsigned long long ka = k.ka, kb = k.kb;
+  sort64_abs(ka, kb, lane);
+  const unsigned long long ma = ka >> 1, mb = kb >> 1;
+  const unsigned long long pa = __shfl_up_sync(FM_FULL, ma, 1);
+  const unsigned long long last_a = __shfl_sync(FM_FULL, ma, 31);
+  unsigned long long pb = __shfl_up_sync(FM_FULL, mb, 1);
+  if (lane == 0) pb = last_a;
+  const uint32_t ba = __ballot_sync(FM_FULL, lane == 0 || pa != ma), bb = __ballot_sync(FM_FULL, pb != mb);
+  uint32_t lo_a, e_a, lo_b, e_b;
+  runs_from_ballots(ba, bb, lane, lo_a, e_a, lo_b, e_b);
+  uint32_t wp = 0, wm = 0, T = 0;
+  if ((uint32_t)lane < r.np) {
+    const uint32_t r2 = lo_a + e_a + 1u, tt = e_a - lo_a;
+    if (ka & 1ull) wm += r2; else wp += r2;
+    T += tt * tt - 1u;
+  }
+  if ((uint32_t)lane + 32u < r.np) {
+    const uint32_t r2 = lo_b + e_b + 1u, tt = e_b - lo_b;
+    if (kb & 1ull) wm += r2; else wp += r2;
+    T += tt * tt - 1u;
+  }
+  r.wp2 = __reduce_add_sync(FM_FULL, wp);
+  r.wm2 = __reduce_add_sync(FM_FULL, wm);
+  r.t = __reduce_add_sync(FM_FULL, T);
+  return r;
+}
+
+struct Tie { uint32_t sq, lin; };   // sum p^2 and MINUS sum p over my keys (T = 3 (sq - lin))
+
+// One search step: if (v < b) addr += imm — a predicated add, no select + add pair.
+template <uint32_t IMM>
+__device__ __forceinline__ void step_lt(uint32_t& addr, float v, float b) {
+  asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %1, %2;\n\t@p add.u32 %0, %0, %3;\n\t}"
+      : "+r"(addr) : "f"(v), "f"(b), "n"(IMM));
+}
+
+// Pass B, first half, for one key: v = what the slot holds.  My own pattern -> my class owns the
+// slot and the returned decrement of its counter is MINUS my arrival number.  No predicates and no
+// branches (ptxas turns a predicated ATOMS into a branch): everybody runs the atomic, with the
+// comparison mask (all ones / zero) as the addend, so a key whose class lost adds nothing to the
+// winner's counter; everybody stores its pattern at the tail of its overflow list (entry k of
+// lane l at list + 128 k + 4 l: conflict-free) and only the losers advance the tail.
+// Returns -(arrival number) mod 2^32 for a member, 0 otherwise.
+__device__ __forceinline__ uint32_t elect_count(uint32_t v, uint32_t bits, uint32_t caddr, uint32_t& lptr) {
+  uint32_t inc, c;
+  asm("set.eq.u32.u32 %0, %1, %2;" : "=r"(inc) : "r"(v), "r"(bits));
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(c) : "r"(caddr), "r"(inc) : "memory");
+  fm_sts_u32(lptr, bits);
+  lptr += 128u & ~inc;
+  return c & inc;
+}
+
+// G baseline keys at a time: position of each in the sorted current row (binary search, the G
+// probe chains interleaved by hand so that their shared-memory latencies overlap) and their
+// election pass B.
+template <int G>
+__device__ __forceinline__ void rank_group(const float* x, uint32_t search_lo, uint32_t search_hi, uint32_t final_k,
+                                           float c31, uint32_t tbl_s, uint32_t c_off, uint32_t mult, uint32_t m,
+                                           uint32_t& acc_all, uint32_t& acc_eq, Tie& tie, uint32_t& lptr) {
+  uint32_t addr[G], h[G], vv[G];
+#pragma unroll
+  for (int k = 0; k < G; ++k) {
+    addr[k] = (c31 < x[k]) ? search_hi : search_lo;
+    h[k] = tbl_s + slot_of(__float_as_uint(x[k]), mult, m);
+  }
+#pragma unroll
+  for (int k = 0; k < G; ++k) vv[k] = fm_lds_u32(h[k]);
+  {
+    float v[G];
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 60u);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<64u>(addr[k], v[k], x[k]);
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 28u);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<32u>(addr[k], v[k], x[k]);
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 12u);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<16u>(addr[k], v[k], x[k]);
+  }
+  uint32_t c[G];
+#pragma unroll
+  for (int k = 0; k < G; ++k) c[k] = elect_count(vv[k], __float_as_uint(x[k]), h[k] + c_off, lptr);
+  {
+    float v[G];
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 4u);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<8u>(addr[k], v[k], x[k]);
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k]);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<4u>(addr[k], v[k], x[k]);
+  }
+  uint2 w[G];
+#pragma unroll
+  for (int k = 0; k < G; ++k) w[k] = lds_v2(final_k + 2u * addr[k]);
+#pragma unroll
+  for (int k = 0; k < G; ++k) { tie.sq += c[k] * c[k]; tie.lin += c[k]; }
+#pragma unroll
+  for (int k = 0; k < G; ++k) {
+    acc_all += w[k].y;
+    if (__uint_as_float(w[k].x) == x[k]) acc_eq += w[k].y;
+  }
+}
+
+// election pass B for one key outside the unrolled groups (current row, overflow rounds)
+__device__ __forceinline__ void classify(uint32_t bits, uint32_t tbl_s, uint32_t c_off, uint32_t mult,
+                                         uint32_t m, Tie& t, uint32_t& lptr) {
+  const uint32_t h = tbl_s + slot_of(bits, mult, m);
+  const uint32_t c = elect_count(fm_lds_u32(h), bits, h + c_off, lptr);
+  t.sq += c * c; t.lin += c;
+}
+
+// vector row c of the staged baseline: lane l takes float4 number l + 32 c (conflict-free).  Returns
+// the index of its first element; k = the four keys (-0 folded onto +0, missing points = the NaN
+// pattern), q = the raw samples.
+__device__ __forceinline__ uint32_t keys4(uint32_t base_s, int c, int lane, uint32_t nb, float nokey, float* k,
+                                          float4& q) {
+  const uint32_t e0 = ((uint32_t)lane + 32u * (uint32_t)c) << 2;
+  q = fm_lds_v4(base_s + (e0 << 2));
+  if (128u * (uint32_t)c + 127u < nb) {                     // warp-uniform: the whole vector row is valid
+    k[0] = q.x + 0.0f; k[1] = q.y + 0.0f; k[2] = q.z + 0.0f; k[3] = q.w + 0.0f;
+  } else {
+    k[0] = e0 < nb ? q.x + 0.0f : nokey;      k[1] = e0 + 1u < nb ? q.y + 0.0f : nokey;
+    k[2] = e0 + 2u < nb ? q.z + 0.0f : nokey; k[3] = e0 + 3u < nb ? q.w + 0.0f : nokey;
+  }
+  return e0;
+}
+
+template <int NV, int NS>
+__global__ void __launch_bounds__(256, 2) k_canary_count(const FmKArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  constexpr uint32_t kCap = 128u * NV + 32u * NS;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int wpc = blockDim.x >> 5;
+  unsigned char* wp = smem + (size_t)warp * a.warp_bytes;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(wp);
+  float* stage = reinterpret_cast<float*>(wp + 16);
+  const uint32_t stage_s = fm_smem_u32(stage), base_s = stage_s + kCur * 4u;
+  const uint32_t search_s = stage_s + (kCur + a.base_cap) * 4u;
+  const uint32_t final_s = search_s + kSearchBytes;
+  const uint32_t tbl_s = final_s + kFinalBytes;
+  const uint32_t m_slots = a.log_m, c_off = 4u * a.log_m;     // a.log_m carries the slot count (a multiple of 4)
+  const fm_global_params& g = a.P->g;
+
+  if (lane == 0) { fm_mbar_init(bar, 1); fm_fence_mbar_init(); }
+  __syncwarp();
+
+  const uint64_t stride = (uint64_t)gridDim.x * wpc;
+  uint64_t s = (uint64_t)blockIdx.x * wpc + warp;
+  uint32_t phase = 0;
+  if (s < a.n_series && lane == 0)
+    issue_rows(a, stage, bar, s, row_len(a.cur_len, s, a.n_cur), row_len(a.base_len, s, a.n_base));
+
+  for (; s < a.n_series; s += stride) {
+    const uint32_t nc = row_len(a.cur_len, s, a.n_cur);
+    const uint32_t nb = row_len(a.base_len, s, a.n_base);
+    const uint64_t sn = s + stride;
+    if (sn < a.n_series) {     // pull the next rows into L2 while this series is ranked
+      const uint32_t nbn = row_len(a.base_len, sn, a.n_base);
+      const char* pb = reinterpret_cast<const char*>(a.base + sn * a.base_pitch);
+      for (uint32_t o = (uint32_t)lane * 128u; o < nbn * 4u; o += 4096u) fm_prefetch_l2(pb + o);
+      if (lane < 2) fm_prefetch_l2(reinterpret_cast<const char*>(a.cur + sn * a.cur_pitch) + lane * 128);
+    }
+    fm_mbar_wait(bar, phase);
+    phase ^= 1u;
+
+    const uint32_t ty = a.metric_type ? a.metric_type[s] : 0u;
+    const fm_type_params tp = a.P->types[ty < a.P->n_types ? ty : 0u];
+    fm_series_rec rec;
+    fm_rec_init(rec);
+    fm_rank_aux ax = {0, 0, 0, 0, 0, 0u, 0u};
+    uint32_t status = 0;
+    if (nc == 0) status |= FM_ST_NO_CURRENT;
+
+    const bool pair = g.pairwise_mode != FM_PW_NONE && nc > 0 && nb > 0;
+    const bool want_mw = pair && fm_mode_has(g.pairwise_mode, FM_PW_MANN_WHITE) && nc >= g.min_mw && nb >= g.min_mw;
+    const bool want_kw = pair && fm_mode_has(g.pairwise_mode, FM_PW_KRUSKAL) && nc >= g.min_kw && nb >= g.min_kw;
+    const bool want_wx = pair && fm_mode_has(g.pairwise_mode, FM_PW_WILCOXON);
+    const bool ranks = want_mw || want_kw;
+    const bool fuse_model = (a.hist == nullptr) && g.ma_mode == FM_MA_ALL;
+
+    // ---- current row (time order for the flags, canonical -0 -> +0 for the ranks) ------------
+    const bool va = (uint32_t)lane < nc, vb = (uint32_t)lane + 32u < nc;
+    const float craw_a = va ? fm_lds_f32(stage_s + 4u * lane) : 0.0f;
+    const float craw_b = vb ? fm_lds_f32(stage_s + 4u * (lane + 32u)) : 0.0f;
+    const float ca = va ? craw_a + 0.0f : CUDART_INF_F;
+    const float cb = vb ? craw_b + 0.0f : CUDART_INF_F;
+
+    // ---- Wilcoxon (pairs need both rows in time order) -----------------------------------------
+    WxInts wx = {0u, 0u, 0u, 0u, false};
+    if (want_wx) wx = wilcoxon_ints(g, wilcoxon_load(g, stage_s, nc, nb, lane), lane);
+    ax.n_wx = wx.np;
+
+    // ---- model on a window / smoothing recurrence reads the staged row in time order ----------
+    bool model_ok = false;
+    if (!a.hist && !fuse_model) model_ok = fm_model(g, stage + kCur, nb, false, lane, rec.mean, rec.sigma);
+
+    // ---- sweep 1 over the staged baseline: moments, election pass A -------------------------------
+    // (the keys are NOT kept: sweep 2 reads the stage again, so that a lane holds four keys at a time)
+    const double pivot = nb ? (double)fm_lds_f32(base_s) : 0.0;
+    FmMom mom = {0.0, 0.0};
+    const float nokey = __uint_as_float(kNoKey);
+    const uint32_t mult0 = mult_of(0);
+    const uint32_t hka = va ? __float_as_uint(ca) : kNoKey, hkb = vb ? __float_as_uint(cb) : kNoKey;
+    if (ranks) {
+      for (uint32_t o = (uint32_t)lane * 16u; o < c_off; o += 512u) sts_zero16(tbl_s + c_off + o);
+      fm_sts_u32(tbl_s + slot_of(hka, mult0, m_slots), hka);
+      fm_sts_u32(tbl_s + slot_of(hkb, mult0, m_slots), hkb);
+    }
+    if (ranks || fuse_model) {
+#pragma unroll
+      for (int c = 0; c < NV; ++c) {
+        float k[4];
+        float4 q;
+        const uint32_t e0 = keys4(base_s, c, lane, nb, nokey, k, q);
+        if (fuse_model) {
+          if (128u * c + 127u < nb) {
+            fm_mom_add(mom, q.x, pivot); fm_mom_add(mom, q.y, pivot);
+            fm_mom_add(mom, q.z, pivot); fm_mom_add(mom, q.w, pivot);
+          } else {
+            if (e0 < nb) fm_mom_add(mom, q.x, pivot);
+            if (e0 + 1u < nb) fm_mom_add(mom, q.y, pivot);
+            if (e0 + 2u < nb) fm_mom_add(mom, q.z, pivot);
+            if (e0 + 3u < nb) fm_mom_add(mom, q.w, pivot);
+          }
+        }
+        if (ranks) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) fm_sts_u32(tbl_s + slot_of(__float_as_uint(k[i]), mult0, m_slots), __float_as_uint(k[i]));
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {
+        const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
+        float v = nokey;
+        if (e < nb) {
+          const float q = fm_lds_f32(base_s + (e << 2));
+          v = q + 0.0f;
+          if (fuse_model) fm_mom_add(mom, q, pivot);
+        }
+        if (ranks) fm_sts_u32(tbl_s + slot_of(__float_as_uint(v), mult0, m_slots), __float_as_uint(v));
+      }
+    }
+    if (a.hist)
+      model_ok = fm_model(g, a.hist + s * a.hist_pitch, row_len(a.hist_len, s, a.n_hist), true, lane, rec.mean, rec.sigma);
+    else if (fuse_model)
+      model_ok = nb >= max(g.min_hist_points, g.ddof + 1u);
+    if (!model_ok) status |= FM_ST_HIST_INSUFFICIENT;
+    double s1 = 0.0, s2 = 0.0;
+    if (fuse_model && model_ok) { s1 = fm_warp_sum(mom.s1); s2 = fm_warp_sum(mom.s2); }
+
+    long long r2c = 0, Tt = 0;
+    if (ranks) {
+      // ---- sorted current row -> search table --------------------------------------------------
+      float sa = ca, sb = cb;
+      sort64(sa, sb, lane);
+      {
+        const float qa = __shfl_up_sync(FM_FULL, sa, 1);
+        const float last_a = __shfl_sync(FM_FULL, sa, 31);
+        float qb = __shfl_up_sync(FM_FULL, sb, 1);
+        if (lane == 0) qb = last_a;
+        const uint32_t ba = __ballot_sync(FM_FULL, lane == 0 || qa != sa), bb = __ballot_sync(FM_FULL, qb != sb);
+        uint32_t lo_a, e_a, lo_b, e_b;
+        runs_from_ballots(ba, bb, lane, lo_a, e_a, lo_b, e_b);
+        // run length counts real samples only (the +inf padding behind position nc is not a sample)
+        const uint32_t rl_a = min(e_a, nc) - min(lo_a, nc), rl_b = min(e_b, nc) - min(lo_b, nc);
+        fm_sts_f32(search_s + 4u * lane, sa);
+        fm_sts_f32(search_s + 4u * (lane + 33u), sb);
+        sts_v2(final_s + 8u * lane, __float_as_uint(sa), (rl_a << 16) | (2u * lane));
+        sts_v2(final_s + 8u * (lane + 33u), __float_as_uint(sb), (rl_b << 16) | (2u * (lane + 32u)));
+      }
+      const float c31 = __shfl_sync(FM_FULL, sa, 31);
+
+      // ---- sweep 2: every key's place in the sorted current row + election pass B ---------------
+      // The overflow lists grow into the stage BEHIND the read position: a lane has produced at most
+      // one entry per key it has consumed, entry k of a lane sits in stage word 32 k + lane, and the
+      // 2 + 4 c + 4 rows of 32 words behind vector row c have been read by every lane by then.
+      __syncwarp();                                         // pass A and the search table are complete
+      Tie tie = {0u, 0u};
+      const uint32_t list0 = stage_s + 4u * lane;
+      uint32_t lptr = list0;
+      uint32_t acc_all = 0, acc_eq = 0;
+      const uint32_t final_k = final_s - 2u * search_s;     // entry address = final_k + 2 * probe address
+      classify(hka, tbl_s, c_off, mult0, m_slots, tie, lptr);
+      classify(hkb, tbl_s, c_off, mult0, m_slots, tie, lptr);
+#pragma unroll
+      for (int c = 0; c < NV; ++c) {
+        float k[4];
+        float4 q;
+        keys4(base_s, c, lane, nb, nokey, k, q);
+        rank_group<4>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
+      }
+      if (NS > 0) {
+        float k[NS > 0 ? NS : 1];
+#pragma unroll
+        for (int j = 0; j < NS; ++j) {
+          const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
+          k[j] = e < nb ? fm_lds_f32(base_s + (e << 2)) + 0.0f : nokey;
+        }
+        rank_group<(NS > 0 ? NS : 1)>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all,
+                                      acc_eq, tie, lptr);
+      }
+
+      // ---- overflow rounds -------------------------------------------------------------------------
+      uint32_t n_l = (lptr - list0) >> 7;
+      unsigned long long t_extra = 0;
+      for (uint32_t round = 1;; ++round) {
+        if (__reduce_max_sync(FM_FULL, n_l) == 0u) break;
+        __syncwarp();                                       // the previous pass B is complete
+        if (round == kMaxRounds) {
+          // Not reached in practice.  What is left are whole classes: count each key's class directly.
+          fm_sts_u32(search_s + 4u * lane, n_l);
+          __syncwarp();
+          for (uint32_t k = 0; k < n_l; ++k) {
+            const uint32_t mine = fm_lds_u32(list0 + 128u * k);
+            uint32_t t = 0;
+            for (uint32_t l2 = 0; l2 < 32u; ++l2) {
+              const uint32_t n2 = fm_lds_u32(search_s + 4u * l2);
+              for (uint32_t k2 = 0; k2 < n2; ++k2) t += fm_lds_u32(stage_s + 4u * l2 + 128u * k2) == mine;
+            }
+            t_extra += (unsigned long long)t * t - 1ull;
+          }
+          break;
+        }
+        for (uint32_t o = (uint32_t)lane * 16u; o < c_off; o += 512u) sts_zero16(tbl_s + c_off + o);
+        const uint32_t mult = mult_of(round);
+        for (uint32_t k = 0; k < n_l; ++k) {
+          const uint32_t bits = fm_lds_u32(list0 + 128u * k);
+          fm_sts_u32(tbl_s + slot_of(bits, mult, m_slots), bits);
+        }
+        __syncwarp();
+        uint32_t wptr = list0;
+        for (uint32_t k = 0; k < n_l; ++k)                  // in-place: wptr never passes the read position
+          classify(fm_lds_u32(list0 + 128u * k), tbl_s, c_off, mult, m_slots, tie, wptr);
+        n_l = (wptr - list0) >> 7;
+      }
+
+      // ---- integers ---------------------------------------------------------------------------------
+      const uint32_t sum_lu = __reduce_add_sync(FM_FULL, (acc_all & 0xFFFFu) + (acc_eq >> 16));
+      r2c = (long long)nc * (nc + 1) + 2ll * nc * nb - (long long)sum_lu;
+      const unsigned long long tl = (unsigned long long)tie.sq + (0u - tie.lin);
+      const unsigned long long t3 = (unsigned long long)__reduce_add_sync(FM_FULL, (uint32_t)(tl & 0xFFFFu)) +
+                                    ((unsigned long long)__reduce_add_sync(FM_FULL, (uint32_t)(tl >> 16)) << 16);
+      const unsigned long long ninv = (unsigned long long)(kCap - nb) + (64u - nc);
+      Tt = (long long)(3ull * t3 + (unsigned long long)fm_warp_sum((long long)t_extra) - (ninv * ninv * ninv - ninv));
+      ax.r2_cur = r2c; ax.t_mw = Tt;
+    }
+
+    // the stage (rows, then lists) has been consumed: hand it to the TMA unit for the next series
+    __syncwarp();
+    if (sn < a.n_series) {
+      fm_fence_proxy_async();
+      if (lane == 0)
+        issue_rows(a, stage, bar, sn, row_len(a.cur_len, sn, a.n_cur), row_len(a.base_len, sn, a.n_base));
+    }
+
+    // ---- a5: every statistic as num * sqrt(Q / P), one lane each ---------------------------------
+    const double dn1 = (double)nc, dn2 = (double)nb, N = dn1 + dn2, dT = (double)Tt;
+    const bool run_mw = want_mw, run_kw = want_kw, run_wx = wx.run;
+    double Q = 0.0, P = 1.0, num = 0.0;
+    double u1 = 0.0, wmin = 0.0;
+    if (run_mw) {
+      u1 = 0.5 * (double)(r2c - (long long)nc * ((long long)nc + 1));
+      const double u2 = dn1 * dn2 - u1, u = u1 > u2 ? u1 : u2;
+      if (lane == 0) {
+        num = u - 0.5 * dn1 * dn2 - (g.cc_mw ? 0.5 : 0.0);
+        P = dn1 * dn2 * ((N + 1.0) * N * (N - 1.0) - dT);          // 12 N (N-1) var
+        Q = 6.0 * N * (N - 1.0);
+      }
+    }
+    if (run_wx) {
+      ax.w2_plus = wx.wp2; ax.w2_minus = wx.wm2; ax.t_wx = wx.t;
+      const double dn = (double)wx.np;
+      wmin = 0.5 * (double)min(wx.wp2, wx.wm2);
+      if (lane == 1) {
+        num = wmin - dn * (dn + 1.0) * 0.25;
+        if (g.cc_wx && num != 0.0) num += 0.5;
+        num = fabs(num);
+        P = 2.0 * dn * (dn + 1.0) * (2.0 * dn + 1.0) - (double)wx.t;   // 48 var
+        Q = 24.0;
+      }
+    }
+    if (run_kw && lane == 2) {
+      const long long Ni = (long long)nc + nb, r2y = Ni * (Ni + 1) - r2c;
+      const long long A = 3ll * (r2c * r2c * (long long)nb + r2y * r2y * (long long)nc) -
+                          3ll * (Ni + 1) * (Ni + 1) * Ni * (long long)nc * (long long)nb;
+      num = 1.0;
+      P = dn1 * dn2 * (N * N * N - N - dT);
+      Q = 0.5 * (double)A * (N - 1.0);                                 // Q / P = H / 2
+    }
+    if (fuse_model && model_ok) {
+      if (lane == 3) {
+        const double m2n = s2 * dn2 - s1 * s1;
+        Q = (nb > g.ddof && m2n > 0.0) ? m2n : 0.0;
+        P = nb > g.ddof ? dn2 * (double)(nb - g.ddof) : 1.0;
+      }
+      if (lane == 4) { Q = s1; P = dn2; }
+    }
+    const bool deg = !(P > 0.0);                                        // zero variance: p = 1
+    const double q = deg ? 0.0 : Q / P;
+    const double rt = sqrt(q);
+    double arg = num * rt;
+    if (lane == 2) arg = q > 0.0 ? rt : -1.0;                          // chi2 sf, 1 dof; H <= 0 -> 1
+    double pe = erfc(arg);
+    pe = (pe > 1.0 || deg) ? 1.0 : pe;
+    const uint32_t degb = __ballot_sync(FM_FULL, deg);
+    const double p_mw = __shfl_sync(FM_FULL, pe, 0), p_wx = __shfl_sync(FM_FULL, pe, 1),
+                 p_kw = __shfl_sync(FM_FULL, pe, 2);
+    const double h_kw = 2.0 * __shfl_sync(FM_FULL, q, 2);
+    if (fuse_model && model_ok) {
+      rec.sigma = __shfl_sync(FM_FULL, rt, 3);
+      rec.mean = pivot + __shfl_sync(FM_FULL, q, 4);
+    }
+    const bool d_mw = run_mw && (degb & 1u), d_wx = run_wx && (degb & 2u), d_kw = run_kw && (degb & 4u);
+    if (run_mw) { rec.u1 = u1; rec.p_u = p_mw; status |= FM_ST_MW_RUN; }
+    if (run_wx) { rec.w = wmin; rec.p_w = p_wx; status |= FM_ST_WX_RUN; }
+    if (run_kw) { rec.h = d_kw ? 0.0 : h_kw; rec.p_h = p_kw; status |= FM_ST_KW_RUN; }
+    if (d_mw || d_wx || d_kw) status |= FM_ST_DEGENERATE;
+
+    bool differ = false;
+    if (pair) {   // A.6 over the evaluated, non-degenerate tests
+      const bool e0 = run_mw && !d_mw, e1 = run_wx && !d_wx, e2 = run_kw && !d_kw;
+      const bool f0 = p_mw < g.alpha, f1 = p_wx < g.alpha, f2 = p_kw < g.alpha;
+      const bool any = (e0 && f0) || (e1 && f1) || (e2 && f2);
+      const bool all = (!e0 || f0) && (!e1 || f1) && (!e2 || f2);
+      if (!(e0 || e1 || e2)) status |= FM_ST_PAIRWISE_SKIPPED;
+      else differ = g.pairwise_mode == FM_PW_ALL ? all : any;
+      if (differ) status |= FM_ST_DIFFER;
+    }
+    if (model_ok && nc > 0) {   // A.7 / A.8
+      const double k = differ ? tp.k_low : tp.k;
+      const double up = __dadd_rn(rec.mean, __dmul_rn(k, rec.sigma));
+      double lo = __dsub_rn(rec.mean, __dmul_rn(k, rec.sigma));
+      if (lo < tp.min_lower_bound) lo = tp.min_lower_bound;
+      rec.upper = up; rec.lower = lo;
+      const double xa = (double)craw_a, xb = (double)craw_b;
+      const bool fa = va && (((tp.bound_mask & 1u) && xa > up) || ((tp.bound_mask & 2u) && xa < lo));
+      const bool fb = vb && (((tp.bound_mask & 1u) && xb > up) || ((tp.bound_mask & 2u) && xb < lo));
+      const uint32_t ma = __ballot_sync(FM_FULL, fa), mb = __ballot_sync(FM_FULL, fb);
+      const uint64_t mask = (uint64_t)ma | ((uint64_t)mb << 32);
+      const uint32_t cnt = (uint32_t)__popc(ma) + (uint32_t)__popc(mb);
+      rec.n_anom = cnt;
+      rec.first_idx = (uint16_t)(mask ? (uint32_t)__ffsll((long long)mask) - 1u : 0xFFFFu);
+      rec.anom_mask = mask;
+      rec.verdict = (cnt >= g.min_anomaly_points && cnt > 0) ? FM_UNHEALTHY : FM_HEALTHY;
+    }
+    if (status & (FM_ST_NO_CURRENT | FM_ST_HIST_INSUFFICIENT)) rec.verdict = FM_UNKNOWN;
+    rec.status = (uint8_t)status;
+    if (lane == 0) {
+      fm_write_record(a.out, s, a.record_kind, rec);
+      if (a.aux) a.aux[s] = ax;
+      if (a.api && a.api_id) fm_rollup_add(a.api, a.api_id[s], rec.verdict);
+    }
+    __syncwarp();
+  }
+}
+
+template <int NV, int NS>
+cudaError_t smem_attr(int bytes) {
+  return cudaFuncSetAttribute(k_canary_count<NV, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+}  // namespace
+
+// tiers (vector rows, scalar rows) -> capacity 128 NV + 32 NS baseline points
+#define FM_COUNT_TIERS(X) X(1, 0) X(2, 0) X(4, 0) X(8, 0) X(11, 1) X(12, 0) X(16, 0)
+
+cudaError_t fm_canary_count_smem_attr(int bytes) {
+  cudaError_t e = cudaSuccess;
+#define X(NV, NS) if (e == cudaSuccess) e = smem_attr<NV, NS>(bytes);
+  FM_COUNT_TIERS(X)
+#undef X
+  return e;
+}
+
+// smallest tier that holds n_base points; 0 if none does
+uint32_t fm_canary_count_tier(uint32_t n_base, int* nv, int* ns) {
+#define X(NV, NS) if (n_base <= 128u * NV + 32u * NS) { *nv = NV; *ns = NS; return 128u * NV + 32u * NS; }
+  FM_COUNT_TIERS(X)
+#undef X
+  return 0;
+}
+
+size_t fm_canary_count_fixed_bytes() { return 16 + kSearchBytes + kFinalBytes; }
+
+int fm_launch_canary_count(const FmKArgs& a, int nv, int ns, int warps_per_cta, int grid, cudaStream_t st) {
+  const size_t smem = (size_t)warps_per_cta * a.warp_bytes;
+  const dim3 block(warps_per_cta * 32);
+#define X(NV, NS) if (nv == NV && ns == NS) { k_canary_count<NV, NS><<<grid, block, smem, st>>>(a); return 1; }
+  FM_COUNT_TIERS(X)
+#undef X
+  return 0;
+}

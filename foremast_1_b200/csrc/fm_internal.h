@@ -35,7 +35,7 @@ struct FmKArgs {
   uint32_t wx_n;           // doubles, raw differences (max pairs)
   uint32_t n_stages;       // 1 or 2 staging buffers per warp
   uint32_t warp_bytes;     // bytes of shared memory per warp
-  uint32_t log_m;          // k_canary_elect: log2 of the election table size
+  uint32_t log_m;          // k_canary_elect: log2 of the election table size; k_canary_count: its slot count
 };
 
 struct FmGArgs {
@@ -62,6 +62,11 @@ int fm_launch_groups_sort(const FmGArgs& a, uint32_t* defer_list, uint32_t* defe
 int fm_launch_canary_sort(const FmKArgs& a, int regs, int valid_regs, int warps_per_cta, int grid, cudaStream_t st);
 cudaError_t fm_canary_sort_smem_attr(int bytes);
 int fm_launch_canary_elect(const FmKArgs& a, int nv, int grid, cudaStream_t st);
+// fm_canary_count.cu: tier = (vector rows, scalar rows) per lane; a.log_m carries the slot count
+int fm_launch_canary_count(const FmKArgs& a, int nv, int ns, int warps_per_cta, int grid, cudaStream_t st);
+uint32_t fm_canary_count_tier(uint32_t n_base, int* nv, int* ns);
+size_t fm_canary_count_fixed_bytes();
+cudaError_t fm_canary_count_smem_attr(int bytes);
 size_t fm_canary_elect_fixed_bytes();
 int fm_launch_ma_only(const FmKArgs& a, int group, int grid, cudaStream_t st);
 cudaError_t fm_canary_elect_smem_attr(int bytes);

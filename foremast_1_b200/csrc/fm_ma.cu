@@ -170,8 +170,7 @@ __global__ void __launch_bounds__(256, 4) k_ma_only(const FmKArgs a) {
 }  // namespace
 
 int fm_launch_ma_only(const FmKArgs& a, int group, int grid, cudaStream_t st) {
-  if (group == 2) k_ma_only<2><<<grid, 256, 0, st>>>(a);
-  else if (group == 4) k_ma_only<4><<<grid, 256, 0, st>>>(a);
+  if (group == 4) k_ma_only<4><<<grid, 256, 0, st>>>(a);
   else if (group == 8) k_ma_only<8><<<grid, 256, 0, st>>>(a);
   else if (group == 16) k_ma_only<16><<<grid, 256, 0, st>>>(a);
   else k_ma_only<32><<<grid, 256, 0, st>>>(a);

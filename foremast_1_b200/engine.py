@@ -55,11 +55,30 @@ class Context:
         self._h = h
         self.device = device
         self.g, self.table = A.default_params()
+        self._pinned = {}          # role -> Pinned, grow-only (pinned_rows)
 
     def close(self):
         if getattr(self, "_h", None):
+            for p in self._pinned.values():
+                p.free()
+            self._pinned = {}
             self._lib.fm_ctx_destroy(self._h)
             self._h = None
+
+    def pinned_rows(self, role, shape):
+        """A zeroed fp32 matrix of `shape` in pinned host memory (fm_alloc_pinned), reused between
+        calls with the same role: what the job loop packs fetched rows into, so that fm_score_batch
+        copies them to the device without a staging copy."""
+        need = int(shape[0]) * int(shape[1])
+        p = self._pinned.get(role)
+        if p is None or p.array.size < need:
+            if p is not None:
+                p.free()
+            p = Pinned((max(need, 1024) * 3 // 2,), np.float32)
+            self._pinned[role] = p
+        m = p.array[:need].reshape(shape)
+        m[...] = 0
+        return m
 
     def __enter__(self):
         return self

@@ -4,6 +4,7 @@ that answers with the CPU oracle, so only the host code is under test here; the
 same flow against the real library is tests/test_gpu_brain.py."""
 import ctypes as C
 import json
+import re
 
 import numpy as np
 import pytest
@@ -11,6 +12,7 @@ import pytest
 import oracle_lib as O
 from foremast_1_b200 import _abi as A
 from foremast_1_b200 import brain as B
+from foremast_1_b200 import gauges as gauges_mod
 from foremast_1_b200.engine import _as_matrix
 
 
@@ -103,8 +105,15 @@ def test_decode_query_range_drops_gaps_and_merges_pods():
         {"metric": {"pod": "b"}, "values": [[130, "7"], [190, "+Inf"]]}]}})
     res = B.decode_query_range(body)
     assert [r[2].tolist() for r in res] == [[1.5, 2.5], [7.0]]
+    # several pods: one row per alias on the 60 s grid, mean over the pods that reported there
+    # (samples at 100 and 130 both snap to grid point 120; 160 and 190 are gaps and stay gaps)
     ts, x = B.merge_series(res)
-    assert ts.tolist() == [100, 130, 220] and x.tolist() == [1.5, 7.0, 2.5]
+    assert ts.tolist() == [120, 240] and x.tolist() == [4.25, 2.5]
+    # one pod, on-grid timestamps (what Prometheus returns for the reference's step-aligned
+    # queries, metricsquery.go:43-46): untouched; a duplicate slot keeps its last sample
+    one = [({}, np.array([60, 120, 120, 300], np.int64), np.array([1, 2, 3, 4], np.float32))]
+    ts, x = B.merge_series(one)
+    assert ts.tolist() == [60, 120, 300] and x.tolist() == [1.0, 3.0, 4.0]
     assert B.decode_query_range(json.dumps(body))[0][2].tolist() == [1.5, 2.5]   # double-encoded proxy reply
     with pytest.raises(ValueError):
         B.decode_query_range('{"status":"error","error":"boom"}')
@@ -115,24 +124,24 @@ def make_docs():
     rng = np.random.default_rng(0)
     hist = rng.normal(100, 5, 600)
     store = {
-        "http://p/h_lat": prom(0, hist), "http://p/b_lat": prom(40000, rng.normal(100, 5, 60)),
-        "http://p/c_lat_ok": prom(50000, rng.normal(100, 5, 30)),
-        "http://p/c_lat_bad": prom(50000, np.concatenate([rng.normal(100, 5, 28), [400.0, 420.0]])),
-        "http://p/h_err": prom(0, rng.integers(0, 3, 600) / 60), "http://p/c_err": prom(50000, rng.integers(0, 3, 30) / 60),
+        "http://p/h_lat": prom(0, hist), "http://p/b_lat": prom(39960, rng.normal(100, 5, 60)),
+        "http://p/c_lat_ok": prom(49980, rng.normal(100, 5, 30)),
+        "http://p/c_lat_bad": prom(49980, np.concatenate([rng.normal(100, 5, 28), [400.0, 420.0]])),
+        "http://p/h_err": prom(0, rng.integers(0, 3, 600) / 60), "http://p/c_err": prom(49980, rng.integers(0, 3, 30) / 60),
         "http://p/empty": json.dumps({"status": "success", "data": {"result": []}}),
     }
     docs = [
-        {"id": "ok", "strategy": "canary", "status": "initial", "modified_at": 0.0,
+        {"id": "ok", "strategy": "canary", "status": "initial", "modified_at": "2018-11-03T16:00:00Z",
          "currentConfig": B.format_config({"latency": "http://p/c_lat_ok", "error5xx": "http://p/c_err"}),
          "baselineConfig": B.format_config({"latency": "http://p/b_lat"}),
          "historicalConfig": B.format_config({"latency": "http://p/h_lat", "error5xx": "http://p/h_err"})},
-        {"id": "bad", "strategy": "rollingUpdate", "status": "initial", "modified_at": 0.0,
+        {"id": "bad", "strategy": "rollingUpdate", "status": "initial", "modified_at": "2018-11-03T16:00:00Z",
          "currentConfig": B.format_config({"latency": "http://p/c_lat_bad"}), "baselineConfig": "",
          "historicalConfig": B.format_config({"latency": "http://p/h_lat"})},
-        {"id": "nocur", "strategy": "continuous", "status": "initial", "modified_at": 0.0,
+        {"id": "nocur", "strategy": "continuous", "status": "initial", "modified_at": "2018-11-03T16:00:00Z",
          "currentConfig": B.format_config({"latency": "http://p/empty"}), "baselineConfig": "",
          "historicalConfig": B.format_config({"latency": "http://p/h_lat"})},
-        {"id": "broken", "strategy": "canary", "status": "initial", "modified_at": 0.0,
+        {"id": "broken", "strategy": "canary", "status": "initial", "modified_at": "2018-11-03T16:00:00Z",
          "currentConfig": B.format_config({"latency": "http://p/404"}), "baselineConfig": "", "historicalConfig": ""},
     ]
     return docs, (lambda url: store[url])
@@ -144,7 +153,7 @@ def check_scored(res):
     assert res["bad"]["status"] == B.ST_UNHEALTH
     info = json.loads(res["bad"]["anomalyInfo"])
     vals = info["latency"]["values"]          # [t0, v0, t1, v1] (Barrelman.go:593-620)
-    assert vals == [50000 + 28 * 60, 400.0, 50000 + 29 * 60, 420.0]
+    assert vals == [49980 + 28 * 60, 400.0, 49980 + 29 * 60, 420.0]
     assert "latency: 2 anomalous" in res["bad"]["reason"]
     assert res["nocur"]["status"] == B.ST_UNKNOWN and "no current metric" in res["nocur"]["reason"]
     assert res["broken"]["status"] == B.ST_PRE_FAILED and "KeyError" in res["broken"]["reason"]
@@ -155,60 +164,198 @@ def test_score_documents_statuses_and_anomaly_info():
     check_scored(B.score_documents(OracleCtx(), docs, fetch))
 
 
+T0 = 1541260800.0          # 2018-11-03T16:00:00Z
+RFC3339_UTC = re.compile(r"^\d{4}-\d\d-\d\dT\d\d:\d\d:\d\d(\.\d{1,9})?Z$")
+
+
+def test_go_time_round_trip():
+    """time.Time as json.Marshal writes it (models.go:86-89) and as common.StrToTime reads the
+    request's startTime / endTime (timeutils.go:9-19)."""
+    assert B.parse_go_time("2018-11-03T16:00:00Z") == T0
+    assert B.parse_go_time("2018-11-03T09:00:00-07:00") == T0
+    assert B.parse_go_time("2018-11-03T16:00:00.123456789Z") == pytest.approx(T0 + 0.123456789, abs=1e-6)
+    assert B.parse_go_time("0001-01-01T00:00:00Z") is None          # Go's zero time: "not set"
+    assert B.parse_go_time("") is None and B.parse_go_time(None) is None
+    assert B.parse_go_time(12.5) == 12.5                             # stamps of older workers of this package
+    with pytest.raises(ValueError):
+        B.parse_go_time("yesterday")
+    assert B.format_go_time(T0) == "2018-11-03T16:00:00Z"            # zero fraction is left out
+    assert B.format_go_time(T0 + 0.25) == "2018-11-03T16:00:00.25Z"  # trailing zeros trimmed
+    for t in (T0, T0 + 0.5, T0 + 86399.000001):
+        assert B.parse_go_time(B.format_go_time(t)) == pytest.approx(t, abs=1e-6)
+        assert RFC3339_UTC.match(B.format_go_time(t))
+
+
 def test_worker_claim_takeover_and_fail_fast():
     docs, fetch = make_docs()
     for d in docs:
-        d["endTime"] = 1000.0
-    docs.append(dict(docs[0], id="stuck", status=B.ST_PRE_INPROGRESS, modified_at=5.0))
-    docs.append(dict(docs[0], id="busy", status=B.ST_PRE_INPROGRESS, modified_at=95.0))
+        d["endTime"] = B.format_go_time(T0 + 1000)
+    docs.append(dict(docs[0], id="stuck", status=B.ST_PRE_INPROGRESS, modified_at=B.format_go_time(T0 + 5)))
+    docs.append(dict(docs[0], id="busy", status=B.ST_POST_INPROGRESS, modified_at=B.format_go_time(T0 + 95)))
     store = B.MemoryStore(docs)
-    clock = [100.0]
+    clock = [T0 + 100.0]
     w = B.BrainWorker(OracleCtx(), store, fetch, env=DEPLOYED_ENV, now=lambda: clock[0])
     res = w.poll_once()
     # "stuck" (95 s old) is taken over, "busy" (5 s old) is left to its owner
-    assert "stuck" in res and "busy" not in res and store.docs["busy"]["status"] == B.ST_PRE_INPROGRESS
+    assert "stuck" in res and "busy" not in res and store.docs["busy"]["status"] == B.ST_POST_INPROGRESS
     # fail fast: unhealthy completes now; healthy before endTime goes back to the queue
     assert store.docs["bad"]["status"] == B.ST_UNHEALTH
     assert store.docs["ok"]["status"] == B.ST_INITIAL and res["ok"]["status"] == B.ST_HEALTH
     assert store.docs["nocur"]["status"] == B.ST_UNKNOWN
-    clock[0] = 2000.0
+    assert store.docs["broken"]["status"] == B.ST_PRE_FAILED and "KeyError" in store.docs["broken"]["reason"]
+    # no time field is ever written as a number
+    for d in store.docs.values():
+        assert isinstance(d["modified_at"], str) and RFC3339_UTC.match(d["modified_at"]), d
+    clock[0] = T0 + 2000.0
     res = w.poll_once()
     assert store.docs["ok"]["status"] == B.ST_HEALTH and B.external_status(store.docs["ok"]["status"]) == "success"
     assert "bad" not in res                       # completed documents are not re-scored
     # an optimistic-lock loser does not claim
-    assert store.update("ok", expect_modified_at=-1.0, status="x") is False
+    assert store.update("ok", expect_modified_at="1999-01-01T00:00:00Z", status="x") is False
+    assert w.errors == []
+
+
+class FakeES:
+    """The two Elasticsearch calls of ElasticsearchStore over a dict of _source documents; keeps the
+    order of the statuses every document went through."""
+
+    def __init__(self, docs):
+        self.docs = docs
+        self.calls, self.trail = [], {k: [] for k in docs}
+        self.fail_ids = set()
+
+    def __call__(self, method, url, body):
+        self.calls.append((method, url, body))
+        if url.endswith("/documents/_search"):
+            want = set(body["query"]["terms"]["status"])
+            hits = [{"_id": k, "_source": dict(v)} for k, v in self.docs.items() if v["status"] in want]
+            return {"hits": {"hits": hits[: body["size"]]}}
+        doc_id = url.split("/")[-2]
+        if doc_id in self.fail_ids:
+            raise OSError("connection reset")
+        p = body["script"]["params"] if "script" in body else {"expect": None, "doc": body["doc"]}
+        if p["expect"] is not None and self.docs[doc_id]["modified_at"] != p["expect"]:
+            return {"result": "noop"}
+        self.docs[doc_id].update(p["doc"])
+        if "status" in p["doc"]:
+            self.trail[doc_id].append(p["doc"]["status"])
+        return {"result": "updated"}
 
 
 def test_elasticsearch_store_speaks_the_documents_index():
-    """ElasticsearchStore against a fake transport: search by status, optimistic update."""
-    from foremast_1_b200 import brain
-    docs = {"a1": {"status": "initial", "modified_at": 5.0, "appName": "x"},
-            "b2": {"status": "completed_health", "modified_at": 6.0}}
-    calls = []
-
-    def transport(method, url, body):
-        calls.append((method, url, body))
-        if url.endswith("/documents/_search"):
-            want = set(body["query"]["terms"]["status"])
-            hits = [{"_id": k, "_source": dict(v)} for k, v in docs.items() if v["status"] in want]
-            return {"hits": {"hits": hits[: body["size"]]}}
-        doc_id = url.split("/")[-2]
-        p = body["script"]["params"] if "script" in body else {"expect": None, "doc": body["doc"]}
-        if p["expect"] is not None and docs[doc_id]["modified_at"] != p["expect"]:
-            return {"result": "noop"}
-        docs[doc_id].update(p["doc"])
-        return {"result": "updated"}
-
-    st = brain.ElasticsearchStore("http://es:9200/", transport=transport)
+    """ElasticsearchStore against a fake transport: search by status, optimistic update on the
+    RFC3339 stamp."""
+    es = FakeES({"a1": {"status": "initial", "modified_at": "2018-11-03T16:00:05Z", "appName": "x"},
+                 "b2": {"status": "completed_health", "modified_at": "2018-11-03T16:00:06Z"}})
+    st = B.ElasticsearchStore("http://es:9200/", transport=es)
     got = st.by_status({"initial", "preprocess_inprogress"})
     assert [d["id"] for d in got] == ["a1"] and got[0]["appName"] == "x"
-    assert calls[0][1] == "http://es:9200/documents/_search"
-    assert st.update("a1", expect_modified_at=5.0, status="preprocess_inprogress", modified_at=9.0)
-    assert docs["a1"]["status"] == "preprocess_inprogress"
-    assert not st.update("a1", expect_modified_at=5.0, status="initial", modified_at=10.0)   # lost the race
-    assert calls[-1][1] == "http://es:9200/documents/document/a1/_update"
+    assert es.calls[0][1] == "http://es:9200/documents/_search"
+    assert st.update("a1", expect_modified_at="2018-11-03T16:00:05Z", status="preprocess_inprogress",
+                     modified_at="2018-11-03T16:00:09Z")
+    assert es.docs["a1"]["status"] == "preprocess_inprogress"
+    assert not st.update("a1", expect_modified_at="2018-11-03T16:00:05Z", status="initial",
+                         modified_at="2018-11-03T16:00:10Z")   # lost the race
+    assert es.calls[-1][1] == "http://es:9200/documents/document/a1/_update"
     assert st.update("b2", reason="ok")
-    assert docs["b2"]["reason"] == "ok"
+    assert es.docs["b2"]["reason"] == "ok"
+
+
+def test_worker_on_a_go_marshalled_document():
+    """tests/golden/document_go_marshal.json is json.Marshal(models.Document) byte for byte as
+    CreateNewDoc indexes it (elasticsearchstore.go:36-52; field order and names from the struct
+    tags, models.go:83-101): time.Time fields are RFC3339 strings, startTime / endTime keep the
+    offset of the request.  The worker must claim it, walk the states of the diagram, re-queue it
+    while endTime lies ahead, take it over when its owner is stuck, and leave every time field a
+    string that time.Time can unmarshal."""
+    import os
+    raw = open(os.path.join(os.path.dirname(__file__), "golden", "document_go_marshal.json"), "rb").read()
+    src = json.loads(raw)
+    assert list(src)[:6] == ["id", "appName", "created_at", "startTime", "endTime", "modified_at"]
+    docs0, fetch = make_docs()
+    src["currentConfig"], src["baselineConfig"], src["historicalConfig"] = (
+        docs0[0]["currentConfig"], docs0[0]["baselineConfig"], docs0[0]["historicalConfig"])
+    end = B.parse_go_time(src["endTime"])
+    assert end == B.parse_go_time("2018-11-03T16:44:00Z")          # 09:44 at -07:00
+    es = FakeES({src["id"]: dict(src)})
+    store = B.ElasticsearchStore("http://es:9200", transport=es)
+    clock = [B.parse_go_time(src["created_at"]) + 10.0]
+    reg = gauges_mod.GaugeRegistry()
+    w = B.BrainWorker(OracleCtx(), store, fetch, env=DEPLOYED_ENV, now=lambda: clock[0], gauges=reg)
+    res = w.poll_once()
+    did = src["id"]
+    # healthy before endTime: back to the queue, having passed every state of the diagram
+    assert es.trail[did] == [B.ST_PRE_INPROGRESS, B.ST_PRE_COMPLETED, B.ST_POST_INPROGRESS, B.ST_INITIAL]
+    assert res[did]["status"] == B.ST_HEALTH and res[did]["written_status"] == B.ST_INITIAL
+    d = es.docs[did]
+    for f in ("created_at", "startTime", "endTime", "modified_at"):
+        assert isinstance(d[f], str) and B.parse_go_time(d[f]) is not None
+    assert RFC3339_UTC.match(d["modified_at"]) and d["created_at"] == src["created_at"]
+    assert d["endTime"] == src["endTime"] and d["startTime"] == src["startTime"]    # not ours to rewrite
+    # another worker dies holding the job: nothing happens for 90 s, then it is taken over
+    stuck = B.format_go_time(clock[0] + 1.0)
+    d["status"], d["modified_at"] = B.ST_POST_INPROGRESS, stuck
+    clock[0] += 60.0
+    assert w.poll_once() == {}
+    clock[0] += 40.0
+    res = w.poll_once()
+    assert res[did]["written_status"] == B.ST_INITIAL and es.docs[did]["modified_at"] != stuck
+    # endTime reached: the healthy verdict completes the job
+    clock[0] = end + 1.0
+    res = w.poll_once()
+    assert es.docs[did]["status"] == B.ST_HEALTH and res[did]["written_status"] == B.ST_HEALTH
+    assert B.external_status(es.docs[did]["status"]) == "success"          # converter.go:11-30
+    # the bounds of both metrics were published for :8000/metrics
+    text = reg.text()
+    assert "foremastbrain:latency_upper" in text and "foremastbrain:error5xx_lower" in text
+    # a job somebody else took over between scoring and write-back is not overwritten
+    es.docs[did]["status"] = B.ST_INITIAL
+    orig_update = store.update
+
+    def racing_update(doc_id, expect_modified_at=None, **fields):
+        if fields.get("status") in (B.ST_HEALTH, B.ST_UNHEALTH, B.ST_UNKNOWN):
+            es.docs[doc_id]["modified_at"] = "2018-11-03T23:59:59Z"      # the other worker's stamp
+        return orig_update(doc_id, expect_modified_at=expect_modified_at, **fields)
+
+    store.update = racing_update
+    res = w.poll_once()
+    assert res[did]["written_status"] is None and es.docs[did]["status"] == B.ST_POST_INPROGRESS
+    assert w.errors == []
+
+
+def test_one_bad_write_back_does_not_strand_the_batch():
+    docs, fetch = make_docs()
+    es = FakeES({d["id"]: dict(d) for d in docs})
+    es.fail_ids = {"bad"}
+    w = B.BrainWorker(OracleCtx(), B.ElasticsearchStore("http://es:9200", transport=es), fetch, env=DEPLOYED_ENV,
+                      now=lambda: T0 + 100.0)
+    res = w.poll_once()
+    assert es.docs["ok"]["status"] == B.ST_HEALTH and es.docs["nocur"]["status"] == B.ST_UNKNOWN
+    assert "bad" not in res or res["bad"].get("written_status") is None
+    assert w.errors and w.errors[0][0] == "bad"
+
+
+def test_metrics_endpoint_serves_what_the_worker_scored():
+    """GET /metrics (foremast-brain.yaml:87-122: port 8000, path /metrics) returns the gauges the UI
+    plots (metrics.js:14-24): bounds of every judged metric and one _anomaly sample per anomalous
+    point whose value is the point's unix timestamp (App.js:231-241)."""
+    import urllib.request
+    docs, fetch = make_docs()
+    docs[1]["appName"] = "demo"
+    reg = gauges_mod.GaugeRegistry()
+    srv = gauges_mod.MetricsServer(reg, host="127.0.0.1", port=0).start()
+    try:
+        w = B.BrainWorker(OracleCtx(), B.MemoryStore(docs), fetch, env=DEPLOYED_ENV, now=lambda: T0, gauges=reg)
+        w.poll_once()
+        body = urllib.request.urlopen(f"http://127.0.0.1:{srv.port}/metrics", timeout=5).read().decode()
+        assert "# TYPE foremastbrain:latency_upper gauge" in body
+        anomalies = [ln for ln in body.splitlines() if ln.startswith("foremastbrain:latency_anomaly")]
+        assert [int(ln.split()[-1]) for ln in anomalies] == [49980 + 28 * 60, 49980 + 29 * 60]
+        assert 'foremastbrain:latency_anomaly{app="demo"}' in body
+        with pytest.raises(urllib.error.HTTPError):
+            urllib.request.urlopen(f"http://127.0.0.1:{srv.port}/other", timeout=5)
+    finally:
+        srv.stop()
 
 
 def _payload(rng, n_series, n_points, style=0):

@@ -16,17 +16,22 @@ from parity import assert_records_match, bound_masks
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module", params=["auto", "generic", "elect", "elect-1stage"])
+@pytest.fixture(scope="module", params=["auto", "auto-tiny", "sort", "generic", "elect", "elect-1stage"])
 def ctx(request):
-    """auto: the register-sort canary kernel (fm_canary_sort.cu) wherever it applies; elect: the
-    election-multiset canary kernel (fm_canary_elect.cu); generic: the shared-memory sort kernel
-    for everything (FOREMAST_CUDA_PATH is read when the ctx is created)."""
+    """auto: the counting canary kernel (fm_canary_count.cu) wherever it applies; auto-tiny: the same
+    with an election table of 64 slots, so that every series goes through all the overflow rounds and
+    the direct count behind them; sort: the register-sort canary kernel (fm_canary_sort.cu); elect:
+    the CTA-per-series election kernel (fm_canary_elect.cu); generic: the shared-memory sort kernel
+    for everything (the FOREMAST_CUDA_* switches are read when the ctx is created)."""
     import os
-    os.environ["FOREMAST_CUDA_PATH"] = request.param.split("-")[0]
+    name = request.param.split("-")
+    os.environ["FOREMAST_CUDA_PATH"] = name[0]
     os.environ["FOREMAST_CUDA_STAGES"] = "1" if request.param.endswith("1stage") else "0"
+    if request.param.endswith("tiny"):
+        os.environ["FOREMAST_CUDA_SLOTS"] = "64"
     c = Context(0)
-    os.environ.pop("FOREMAST_CUDA_PATH")
-    os.environ.pop("FOREMAST_CUDA_STAGES")
+    for k in ("FOREMAST_CUDA_PATH", "FOREMAST_CUDA_STAGES", "FOREMAST_CUDA_SLOTS"):
+        os.environ.pop(k, None)
     yield c
     c.close()
 
