@@ -218,6 +218,7 @@ int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
   pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * (best_total / best_w), need));
   if (!c->count_smem_set) { FM_CK(c, fm_canary_count_smem_attr((int)limit)); c->count_smem_set = 1; }
   fill_common(c, b, true, a);
+  a.cnt_nv = (uint32_t)nv; a.cnt_ns = (uint32_t)ns;
   pl->fast = true; pl->kind = 5; pl->regs = nv; pl->valid = ns;
   return FM_OK;
 }
@@ -299,7 +300,7 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
 }
 
 int launch_plan(const Plan& pl, cudaStream_t st) {
-  if (pl.kind == 5) return fm_launch_canary_count(pl.a, pl.regs, pl.valid, pl.wpc, pl.grid, st);
+  if (pl.kind == 5) return fm_launch_canary_count(pl.a, pl.wpc, pl.grid, st);
   if (pl.kind == 4) return fm_launch_ma_only(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 3) return fm_launch_canary_elect(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 2) return fm_launch_canary_sort(pl.a, pl.regs, pl.valid, pl.wpc, pl.grid, st);

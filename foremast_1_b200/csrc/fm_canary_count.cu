@@ -186,12 +186,20 @@ __device__ __forceinline__ void rank_group(const float* x, uint32_t search_lo, u
   }
 }
 
-// election pass B for one key outside the unrolled groups (current row, overflow rounds)
-__device__ __forceinline__ void classify(uint32_t bits, uint32_t tbl_s, uint32_t c_off, uint32_t mult,
+// election pass B for G keys that are not searched (current row, overflow rounds); the G chains
+// (slot load, atomic) are in flight together
+template <int G>
+__device__ __forceinline__ void classify(const uint32_t* bits, uint32_t tbl_s, uint32_t c_off, uint32_t mult,
                                          uint32_t m, Tie& t, uint32_t& lptr) {
-  const uint32_t h = tbl_s + slot_of(bits, mult, m);
-  const uint32_t c = elect_count(fm_lds_u32(h), bits, h + c_off, lptr);
-  t.sq += c * c; t.lin += c;
+  uint32_t h[G], v[G], c[G];
+#pragma unroll
+  for (int k = 0; k < G; ++k) h[k] = tbl_s + slot_of(bits[k], mult, m);
+#pragma unroll
+  for (int k = 0; k < G; ++k) v[k] = fm_lds_u32(h[k]);
+#pragma unroll
+  for (int k = 0; k < G; ++k) c[k] = elect_count(v[k], bits[k], h[k] + c_off, lptr);
+#pragma unroll
+  for (int k = 0; k < G; ++k) { t.sq += c[k] * c[k]; t.lin += c[k]; }
 }
 
 // vector row c of the staged baseline: lane l takes float4 number l + 32 c (conflict-free).  Returns
@@ -210,10 +218,20 @@ __device__ __forceinline__ uint32_t keys4(uint32_t base_s, int c, int lane, uint
   return e0;
 }
 
-template <int NV, int NS>
+// The window / smoothing / separate-history forms of the model are a call, not inline code: the
+// series loop stays small enough for the instruction cache.
+struct ModelOut { double mean, sigma; bool ok; };
+__device__ __noinline__ ModelOut model_call(const fm_global_params* g, const float* x, uint32_t n, bool vec_ok, int lane) {
+  ModelOut o;
+  o.ok = fm_model(*g, x, n, vec_ok, lane, o.mean, o.sigma);
+  return o;
+}
+
 __global__ void __launch_bounds__(256, 2) k_canary_count(const FmKArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
-  constexpr uint32_t kCap = 128u * NV + 32u * NS;
+  // tier: NV vector rows (4 keys per lane each) + NS scalar rows of the staged baseline
+  const uint32_t NV = a.cnt_nv, NS = a.cnt_ns;
+  const uint32_t kCap = 128u * NV + 32u * NS;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int wpc = blockDim.x >> 5;
@@ -278,44 +296,60 @@ __global__ void __launch_bounds__(256, 2) k_canary_count(const FmKArgs a) {
 
     // ---- model on a window / smoothing recurrence reads the staged row in time order ----------
     bool model_ok = false;
-    if (!a.hist && !fuse_model) model_ok = fm_model(g, stage + kCur, nb, false, lane, rec.mean, rec.sigma);
+    if (!a.hist && !fuse_model) {
+      const ModelOut mo = model_call(&g, stage + kCur, nb, false, lane);
+      model_ok = mo.ok; rec.mean = mo.mean; rec.sigma = mo.sigma;
+    }
 
     // ---- sweep 1 over the staged baseline: moments, election pass A -------------------------------
-    // (the keys are NOT kept: sweep 2 reads the stage again, so that a lane holds four keys at a time)
+    // (the keys are NOT kept: sweep 2 reads the stage again, so that a lane holds a few keys at a
+    // time and both sweeps are short rolled loops that stay in the instruction cache)
     const double pivot = nb ? (double)fm_lds_f32(base_s) : 0.0;
     FmMom mom = {0.0, 0.0};
     const float nokey = __uint_as_float(kNoKey);
     const uint32_t mult0 = mult_of(0);
     const uint32_t hka = va ? __float_as_uint(ca) : kNoKey, hkb = vb ? __float_as_uint(cb) : kNoKey;
+    const uint32_t nfull = min(NV, nb >> 7);                  // vector rows without a missing point
     if (ranks) {
       for (uint32_t o = (uint32_t)lane * 16u; o < c_off; o += 512u) sts_zero16(tbl_s + c_off + o);
       fm_sts_u32(tbl_s + slot_of(hka, mult0, m_slots), hka);
       fm_sts_u32(tbl_s + slot_of(hkb, mult0, m_slots), hkb);
     }
     if (ranks || fuse_model) {
-#pragma unroll
-      for (int c = 0; c < NV; ++c) {
+#pragma unroll 1
+      for (uint32_t c = 0; c < nfull; ++c) {
+        const float4 q = fm_lds_v4(base_s + (((uint32_t)lane + 32u * c) << 4));
+        if (fuse_model) {
+          fm_mom_add(mom, q.x, pivot); fm_mom_add(mom, q.y, pivot);
+          fm_mom_add(mom, q.z, pivot); fm_mom_add(mom, q.w, pivot);
+        }
+        if (ranks) {
+          const uint32_t k0 = __float_as_uint(q.x + 0.0f), k1 = __float_as_uint(q.y + 0.0f),
+                         k2 = __float_as_uint(q.z + 0.0f), k3 = __float_as_uint(q.w + 0.0f);
+          fm_sts_u32(tbl_s + slot_of(k0, mult0, m_slots), k0);
+          fm_sts_u32(tbl_s + slot_of(k1, mult0, m_slots), k1);
+          fm_sts_u32(tbl_s + slot_of(k2, mult0, m_slots), k2);
+          fm_sts_u32(tbl_s + slot_of(k3, mult0, m_slots), k3);
+        }
+      }
+#pragma unroll 1
+      for (uint32_t c = nfull; c < NV; ++c) {                 // ragged rows: the tail of the row and what lies behind it
         float k[4];
         float4 q;
         const uint32_t e0 = keys4(base_s, c, lane, nb, nokey, k, q);
         if (fuse_model) {
-          if (128u * c + 127u < nb) {
-            fm_mom_add(mom, q.x, pivot); fm_mom_add(mom, q.y, pivot);
-            fm_mom_add(mom, q.z, pivot); fm_mom_add(mom, q.w, pivot);
-          } else {
-            if (e0 < nb) fm_mom_add(mom, q.x, pivot);
-            if (e0 + 1u < nb) fm_mom_add(mom, q.y, pivot);
-            if (e0 + 2u < nb) fm_mom_add(mom, q.z, pivot);
-            if (e0 + 3u < nb) fm_mom_add(mom, q.w, pivot);
-          }
+          if (e0 < nb) fm_mom_add(mom, q.x, pivot);
+          if (e0 + 1u < nb) fm_mom_add(mom, q.y, pivot);
+          if (e0 + 2u < nb) fm_mom_add(mom, q.z, pivot);
+          if (e0 + 3u < nb) fm_mom_add(mom, q.w, pivot);
         }
         if (ranks) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) fm_sts_u32(tbl_s + slot_of(__float_as_uint(k[i]), mult0, m_slots), __float_as_uint(k[i]));
         }
       }
-#pragma unroll
-      for (int j = 0; j < NS; ++j) {
+#pragma unroll 1
+      for (uint32_t j = 0; j < NS; ++j) {
         const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
         float v = nokey;
         if (e < nb) {
@@ -326,9 +360,10 @@ __global__ void __launch_bounds__(256, 2) k_canary_count(const FmKArgs a) {
         if (ranks) fm_sts_u32(tbl_s + slot_of(__float_as_uint(v), mult0, m_slots), __float_as_uint(v));
       }
     }
-    if (a.hist)
-      model_ok = fm_model(g, a.hist + s * a.hist_pitch, row_len(a.hist_len, s, a.n_hist), true, lane, rec.mean, rec.sigma);
-    else if (fuse_model)
+    if (a.hist) {
+      const ModelOut mo = model_call(&g, a.hist + s * a.hist_pitch, row_len(a.hist_len, s, a.n_hist), true, lane);
+      model_ok = mo.ok; rec.mean = mo.mean; rec.sigma = mo.sigma;
+    } else if (fuse_model)
       model_ok = nb >= max(g.min_hist_points, g.ddof + 1u);
     if (!model_ok) status |= FM_ST_HIST_INSUFFICIENT;
     double s1 = 0.0, s2 = 0.0;
@@ -366,24 +401,31 @@ __global__ void __launch_bounds__(256, 2) k_canary_count(const FmKArgs a) {
       uint32_t lptr = list0;
       uint32_t acc_all = 0, acc_eq = 0;
       const uint32_t final_k = final_s - 2u * search_s;     // entry address = final_k + 2 * probe address
-      classify(hka, tbl_s, c_off, mult0, m_slots, tie, lptr);
-      classify(hkb, tbl_s, c_off, mult0, m_slots, tie, lptr);
-#pragma unroll
-      for (int c = 0; c < NV; ++c) {
+      {
+        const uint32_t ck[2] = {hka, hkb};
+        classify<2>(ck, tbl_s, c_off, mult0, m_slots, tie, lptr);
+      }
+      uint32_t c = 0;
+#pragma unroll 1
+      for (; c + 2u <= nfull; c += 2u) {                    // two full vector rows: eight probe chains in flight
+        const float4 q0 = fm_lds_v4(base_s + (((uint32_t)lane + 32u * c) << 4));
+        const float4 q1 = fm_lds_v4(base_s + (((uint32_t)lane + 32u * c + 32u) << 4));
+        const float k[8] = {q0.x + 0.0f, q0.y + 0.0f, q0.z + 0.0f, q0.w + 0.0f,
+                            q1.x + 0.0f, q1.y + 0.0f, q1.z + 0.0f, q1.w + 0.0f};
+        rank_group<8>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
+      }
+#pragma unroll 1
+      for (; c < NV; ++c) {
         float k[4];
         float4 q;
         keys4(base_s, c, lane, nb, nokey, k, q);
         rank_group<4>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
       }
-      if (NS > 0) {
-        float k[NS > 0 ? NS : 1];
-#pragma unroll
-        for (int j = 0; j < NS; ++j) {
-          const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
-          k[j] = e < nb ? fm_lds_f32(base_s + (e << 2)) + 0.0f : nokey;
-        }
-        rank_group<(NS > 0 ? NS : 1)>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all,
-                                      acc_eq, tie, lptr);
+#pragma unroll 1
+      for (uint32_t j = 0; j < NS; ++j) {
+        const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
+        const float k = e < nb ? fm_lds_f32(base_s + (e << 2)) + 0.0f : nokey;
+        rank_group<1>(&k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
       }
 
       // ---- overflow rounds -------------------------------------------------------------------------
@@ -409,14 +451,35 @@ __global__ void __launch_bounds__(256, 2) k_canary_count(const FmKArgs a) {
         }
         for (uint32_t o = (uint32_t)lane * 16u; o < c_off; o += 512u) sts_zero16(tbl_s + c_off + o);
         const uint32_t mult = mult_of(round);
-        for (uint32_t k = 0; k < n_l; ++k) {
-          const uint32_t bits = fm_lds_u32(list0 + 128u * k);
-          fm_sts_u32(tbl_s + slot_of(bits, mult, m_slots), bits);
+        {
+          uint32_t k = 0;
+          for (; k + 4u <= n_l; k += 4u) {
+            uint32_t bits[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) bits[i] = fm_lds_u32(list0 + 128u * (k + i));
+#pragma unroll
+            for (int i = 0; i < 4; ++i) fm_sts_u32(tbl_s + slot_of(bits[i], mult, m_slots), bits[i]);
+          }
+          for (; k < n_l; ++k) {
+            const uint32_t bits = fm_lds_u32(list0 + 128u * k);
+            fm_sts_u32(tbl_s + slot_of(bits, mult, m_slots), bits);
+          }
         }
         __syncwarp();
         uint32_t wptr = list0;
-        for (uint32_t k = 0; k < n_l; ++k)                  // in-place: wptr never passes the read position
-          classify(fm_lds_u32(list0 + 128u * k), tbl_s, c_off, mult, m_slots, tie, wptr);
+        {
+          uint32_t k = 0;                                   // in place: wptr never passes the read position
+          for (; k + 4u <= n_l; k += 4u) {
+            uint32_t bits[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) bits[i] = fm_lds_u32(list0 + 128u * (k + i));
+            classify<4>(bits, tbl_s, c_off, mult, m_slots, tie, wptr);
+          }
+          for (; k < n_l; ++k) {
+            const uint32_t bits = fm_lds_u32(list0 + 128u * k);
+            classify<1>(&bits, tbl_s, c_off, mult, m_slots, tie, wptr);
+          }
+        }
         n_l = (wptr - list0) >> 7;
       }
 
@@ -540,22 +603,15 @@ __global__ void __launch_bounds__(256, 2) k_canary_count(const FmKArgs a) {
   }
 }
 
-template <int NV, int NS>
-cudaError_t smem_attr(int bytes) {
-  return cudaFuncSetAttribute(k_canary_count<NV, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-}
-
 }  // namespace
 
-// tiers (vector rows, scalar rows) -> capacity 128 NV + 32 NS baseline points
+// tiers (vector rows, scalar rows) -> capacity 128 NV + 32 NS baseline points.  The rows are walked
+// by rolled loops, so one kernel serves every tier; a tier only sizes the stage and balances the
+// keys over the lanes (1440 points = 11 vector rows + 1 scalar row = 45 keys in every lane).
 #define FM_COUNT_TIERS(X) X(1, 0) X(2, 0) X(4, 0) X(8, 0) X(11, 1) X(12, 0) X(16, 0)
 
 cudaError_t fm_canary_count_smem_attr(int bytes) {
-  cudaError_t e = cudaSuccess;
-#define X(NV, NS) if (e == cudaSuccess) e = smem_attr<NV, NS>(bytes);
-  FM_COUNT_TIERS(X)
-#undef X
-  return e;
+  return cudaFuncSetAttribute(k_canary_count, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
 // smallest tier that holds n_base points; 0 if none does
@@ -568,11 +624,8 @@ uint32_t fm_canary_count_tier(uint32_t n_base, int* nv, int* ns) {
 
 size_t fm_canary_count_fixed_bytes() { return 16 + kSearchBytes + kFinalBytes; }
 
-int fm_launch_canary_count(const FmKArgs& a, int nv, int ns, int warps_per_cta, int grid, cudaStream_t st) {
+int fm_launch_canary_count(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st) {
   const size_t smem = (size_t)warps_per_cta * a.warp_bytes;
-  const dim3 block(warps_per_cta * 32);
-#define X(NV, NS) if (nv == NV && ns == NS) { k_canary_count<NV, NS><<<grid, block, smem, st>>>(a); return 1; }
-  FM_COUNT_TIERS(X)
-#undef X
-  return 0;
+  k_canary_count<<<grid, warps_per_cta * 32, smem, st>>>(a);
+  return 1;
 }

@@ -36,6 +36,7 @@ struct FmKArgs {
   uint32_t n_stages;       // 1 or 2 staging buffers per warp
   uint32_t warp_bytes;     // bytes of shared memory per warp
   uint32_t log_m;          // k_canary_elect: log2 of the election table size; k_canary_count: its slot count
+  uint32_t cnt_nv, cnt_ns; // k_canary_count: vector rows / scalar rows of the staged baseline per lane
 };
 
 struct FmGArgs {
@@ -63,7 +64,7 @@ int fm_launch_canary_sort(const FmKArgs& a, int regs, int valid_regs, int warps_
 cudaError_t fm_canary_sort_smem_attr(int bytes);
 int fm_launch_canary_elect(const FmKArgs& a, int nv, int grid, cudaStream_t st);
 // fm_canary_count.cu: tier = (vector rows, scalar rows) per lane; a.log_m carries the slot count
-int fm_launch_canary_count(const FmKArgs& a, int nv, int ns, int warps_per_cta, int grid, cudaStream_t st);
+int fm_launch_canary_count(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st);
 uint32_t fm_canary_count_tier(uint32_t n_base, int* nv, int* ns);
 size_t fm_canary_count_fixed_bytes();
 cudaError_t fm_canary_count_smem_attr(int bytes);
