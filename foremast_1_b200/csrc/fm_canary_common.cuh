@@ -114,11 +114,11 @@ __device__ __forceinline__ unsigned long long wx_key(double d) {
 }
 
 __device__ __forceinline__ WxKeys wilcoxon_load(const fm_global_params& g, uint32_t stage_s, uint32_t nc,
-                                                uint32_t nb, int lane) {
+                                                uint32_t nb, int lane, uint32_t base_off = kCur) {
   // key = |d| as an ordered 64-bit integer shifted left by one, bit 0 = (d < 0); zero differences
   // and padding get the largest key so that they sort behind the n' used ones
   WxKeys k = {~0ull, ~0ull, 0u, min(nc, nb)};
-  const uint32_t base_s = stage_s + kCur * 4u;
+  const uint32_t base_s = stage_s + base_off * 4u;     // floats between the two staged rows
   const uint32_t oc = g.pair_rule == FM_PAIR_TAIL ? nc - k.n_pairs : 0u;
   const uint32_t ob = g.pair_rule == FM_PAIR_TAIL ? nb - k.n_pairs : 0u;
   if ((uint32_t)lane < k.n_pairs) {

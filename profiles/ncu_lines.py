@@ -59,11 +59,13 @@ def main():
     per_line = collections.Counter()
     per_line_samples = collections.Counter()
     per_op = collections.Counter()
+    per_line_op = collections.Counter()
     stalls = collections.Counter()
     for (op, where), (op2, n, smp, st) in zip(sass, execd):
         per_line[where] += n
         per_line_samples[where] += smp
         per_op[op.split(".")[0]] += n
+        per_line_op[(where, op.split(".")[0])] += n
         for h, v in st.items():
             stalls[h] += v
     total = sum(per_line.values())
@@ -76,6 +78,11 @@ def main():
     print("\nper opcode:")
     for o, n in per_op.most_common(30):
         print(f"  {n / n_series:8.1f}  {o}")
+    if "--line-ops" in sys.argv:
+        print("\nper (line, opcode), >= 0.3 % of the instructions:")
+        for ((f, l), o), n in sorted(per_line_op.items()):
+            if n >= 0.003 * total:
+                print(f"  {n / n_series:8.1f}  {f}:{l}  {o}")
     print("\nstall samples:")
     for h, v in stalls.most_common(10):
         print(f"  {100.0 * v / tot_s:5.1f} %  {h}")

@@ -16,11 +16,12 @@ from parity import assert_records_match, bound_masks
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module", params=["auto", "auto-tiny", "sort", "generic", "elect", "elect-1stage"])
+@pytest.fixture(scope="module", params=["auto", "auto-tiny", "count1", "count1-tiny", "sort", "generic", "elect", "elect-1stage"])
 def ctx(request):
-    """auto: the counting canary kernel (fm_canary_count.cu) wherever it applies; auto-tiny: the same
-    with an election table of 64 slots, so that every series goes through all the overflow rounds and
-    the direct count behind them; sort: the register-sort canary kernel (fm_canary_sort.cu); elect:
+    """auto: the counting canary kernel with two warps per series (k_canary_pair, fm_canary_count.cu)
+    wherever it applies; count1: its one-warp-per-series form (k_canary_count); -tiny: the same with
+    an election table of 64 slots, so that every series goes through all the overflow rounds and the
+    direct count behind them; sort: the register-sort canary kernel (fm_canary_sort.cu); elect:
     the CTA-per-series election kernel (fm_canary_elect.cu); generic: the shared-memory sort kernel
     for everything (the FOREMAST_CUDA_* switches are read when the ctx is created)."""
     import os
