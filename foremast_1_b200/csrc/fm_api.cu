@@ -52,8 +52,7 @@ struct fm_ctx {
   // Diagnostic switches, read ONCE when the ctx is created (none is needed in production):
   int force_path = 0;              // FOREMAST_CUDA_PATH: generic = 1 (shared-memory sort kernel only),
                                    // sort = 2 (register-sort canary kernel), elect = 3 (CTA-per-series
-                                   // election kernel), count1 = 4 (counting kernel, one warp per series),
-                                   // else 0 = auto (counting kernel, two warps per series, where it applies)
+                                   // election kernel), else 0 = auto (counting kernel where it applies)
   int force_stages = 0;            // FOREMAST_CUDA_STAGES=1|2: staging buffers per warp of the elect path
   int count_slots = 0;             // FOREMAST_CUDA_SLOTS: election-table slots of the counting kernel
   int count_warps = 0;             // FOREMAST_CUDA_WARPS: warps per SM of the counting kernel
@@ -96,7 +95,7 @@ uint32_t round4(uint32_t n) { return (n + 3u) & ~3u; }
 bool mode_has(uint32_t mode, uint32_t t) { return mode == t || mode == FM_PW_ALL || mode == FM_PW_ANY; }
 
 // kind: 0 = k_score_series (generic), 2 = k_canary_sort<regs>, 3 = k_canary_elect<regs>, 4 = k_ma_only<regs>,
-// 5 = k_canary_count (one warp per series), 6 = k_canary_pair (two warps per series)
+// 5 = k_canary_count
 struct Plan { FmKArgs a; int wpc; int grid; bool fast; int kind; int regs; int valid; };
 
 void fill_common(fm_ctx* c, const fm_batch* b, bool canary, FmKArgs& a) {
@@ -205,23 +204,12 @@ int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
   const size_t sm_total = 233472;
   if (!c->count_smem_set) { FM_CK(c, fm_canary_count_smem_attr((int)limit)); c->count_smem_set = 1; }
   fill_common(c, b, true, a);
-  if (c->force_path != 4) {
-    // two warps per series (k_canary_pair): one CTA of 64 threads per series in flight
-    a.warp_bytes = (uint32_t)((fm_canary_pair_fixed_bytes() + (size_t)cap * 4 + (size_t)slots * 8 + 127) & ~size_t(127));
-    if (a.warp_bytes > limit) return fail(c, FM_E_UNSUPPORTED, "canary counting path does not fit shared memory");
-    int ctas = (int)(sm_total / ((size_t)a.warp_bytes + 1024));
-    const int max_ctas = c->count_warps ? std::max(1, c->count_warps / 2) : 14;     // 72 registers per thread
-    ctas = std::max(1, std::min(ctas, max_ctas));
-    pl->wpc = 2;
-    pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * ctas, b->n_series));
-    pl->fast = true; pl->kind = 6; pl->regs = nv; pl->valid = ns;
-    return FM_OK;
-  }
   a.warp_bytes = (uint32_t)((fm_canary_count_fixed_bytes() + (size_t)(64 + cap) * 4 + (size_t)slots * 8 + 127) & ~size_t(127));
   const int max_warps = c->count_warps ? c->count_warps : 16;     // 128 registers per thread
   int best_w = 1, best_total = 0;
-  // FOREMAST_CUDA_STAGES=2 (experiment): ONE CTA per SM whose warps meet at a barrier per series
-  a.n_stages = c->force_stages == 2 ? 2u : 1u;
+  // ONE CTA per SM whose warps meet at a barrier per series, so that they share the instruction
+  // fetches of the long loop body (+4 %); FOREMAST_CUDA_STAGES=1 (experiment): several free-running CTAs
+  a.n_stages = c->force_stages == 1 ? 1u : 2u;
   const int w_hi = a.n_stages == 2u ? 16 : 8, w_lo = a.n_stages == 2u ? 2 : 1;
   for (int w = w_lo; w <= w_hi; ++w) {
     const size_t cta = (size_t)w * a.warp_bytes;
@@ -316,7 +304,6 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
 }
 
 int launch_plan(const Plan& pl, cudaStream_t st) {
-  if (pl.kind == 6) return fm_launch_canary_pair(pl.a, pl.grid, st);
   if (pl.kind == 5) return fm_launch_canary_count(pl.a, pl.wpc, pl.grid, st);
   if (pl.kind == 4) return fm_launch_ma_only(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 3) return fm_launch_canary_elect(pl.a, pl.regs, pl.grid, st);
@@ -422,7 +409,7 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
   c->num_sms = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
   if (const char* e = getenv("FOREMAST_CUDA_PATH"))
-    c->force_path = strcmp(e, "generic") == 0 ? 1 : (strcmp(e, "sort") == 0 ? 2 : (strcmp(e, "elect") == 0 ? 3 : (strcmp(e, "count1") == 0 ? 4 : 0)));
+    c->force_path = strcmp(e, "generic") == 0 ? 1 : (strcmp(e, "sort") == 0 ? 2 : (strcmp(e, "elect") == 0 ? 3 : 0));
   if (const char* e = getenv("FOREMAST_CUDA_STAGES")) c->force_stages = (e[0] == '1') ? 1 : (e[0] == '2' ? 2 : 0);
   if (const char* e = getenv("FOREMAST_CUDA_SLOTS")) { const int v = atoi(e); c->count_slots = (v >= 64 && v <= 8192) ? v : 0; }
   if (const char* e = getenv("FOREMAST_CUDA_WARPS")) { const int v = atoi(e); c->count_warps = (v >= 1 && v <= 32) ? v : 0; }

@@ -335,7 +335,6 @@ __device__ __noinline__ ModelOut model_call(const fm_global_params* g, const flo
   return o;
 }
 
-template <int TNV>
 __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   // tier: NV vector rows (4 keys per lane each) + NS scalar rows of the staged baseline
@@ -446,13 +445,8 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
           fm_sts_u32(tbl_s + slot_of(k3, mult0, m_slots), k3);
         }
       };
-      if (TNV > 0 && nfull == (uint32_t)TNV) {               // the tier's own shape: straight-line code
-#pragma unroll
-        for (int c = 0; c < TNV; ++c) row1((uint32_t)c);
-      } else {
 #pragma unroll 1
-        for (uint32_t c = 0; c < nfull; ++c) row1(c);
-      }
+      for (uint32_t c = 0; c < nfull; ++c) row1(c);
 #pragma unroll 1
       for (uint32_t c = nfull; c < NV; ++c) {                 // ragged rows: the tail of the row and what lies behind it
         float k[4];
@@ -534,14 +528,8 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
                             q1.x + 0.0f, q1.y + 0.0f, q1.z + 0.0f, q1.w + 0.0f};
         rank_group<8>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
       };
-      if (TNV > 0 && nfull == (uint32_t)TNV) {
-#pragma unroll
-        for (int cc = 0; cc + 2 <= TNV; cc += 2) rows2((uint32_t)cc);
-        c = (uint32_t)(TNV & ~1);
-      } else {
 #pragma unroll 1
-        for (; c + 2u <= nfull; c += 2u) rows2(c);
-      }
+      for (; c + 2u <= nfull; c += 2u) rows2(c);
 #pragma unroll 1
       for (; c < NV; ++c) {
         float k[4];
@@ -636,331 +624,6 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
   }
 }
 
-// =================================================================================================
-// k_canary_pair — the same algorithm with TWO warps per series (one CTA of 64 threads per series).
-//
-// One warp per series keeps 15 warps on an SM (15 KB of shared memory each) and leaves the issue
-// slots half empty: the phases are chains of dependent shared-memory and shuffle operations.  Two
-// warps per series share the 15 KB, so an SM holds 30 warps for the same footprint:
-//   warp 0  sorts the current row and builds the search tables, ranks the first half of the
-//           baseline rows, and turns the integers into the record (a5..a9);
-//   warp 1  runs the Wilcoxon test (it is independent of everything else), the separate-history
-//           model if there is one, ranks the second half of the rows, the scalar rows and the
-//           current points, and hands its partial sums over through shared memory.  While warp 0
-//           is in the epilogue of series k, warp 1 is already in the Wilcoxon test of series k + 1.
-// CTA barriers: after pass A, around every overflow round, before the hand-over.  Each warp's
-// overflow lists grow into ITS part of the stage behind its own read position (layout below).
-//
-// Stage (floats): [current 64][pad 32][baseline cap][pad 64]; warp 0 owns [0, 96 + 128 nv0), warp 1
-// the rest (nv0 = vector rows of warp 0).
-constexpr uint32_t kPairCurPad = 96;     // floats before the baseline row
-constexpr uint32_t kPairTailPad = 64;    // floats behind it
-constexpr uint32_t kXchgBytes = 128;
-
-struct PairXchg {                         // warp 1 -> warp 0
-  double s1, s2, mean, sigma;
-  unsigned long long t3, t_extra;
-  uint32_t sum_lu, np, wp2, wm2, twx, flags;   // flags: bit 0 Wilcoxon ran, bit 1 model ok
-};
-
-__device__ __forceinline__ void issue_rows_pair(const FmKArgs& a, float* stage, uint64_t* bar, uint64_t s,
-                                                uint32_t nc, uint32_t nb) {
-  const uint32_t cb = ((nc + 3u) & ~3u) * 4u, bb = ((nb + 3u) & ~3u) * 4u;
-  fm_mbar_expect_tx(bar, cb + bb);
-  if (cb) fm_bulk_g2s(stage, a.cur + s * a.cur_pitch, cb, bar);
-  if (bb) fm_bulk_g2s(stage + kPairCurPad, a.base + s * a.base_pitch, bb, bar);
-}
-
-__global__ void __launch_bounds__(64, 14) k_canary_pair(const FmKArgs a) {
-  extern __shared__ __align__(128) unsigned char smem[];
-  const uint32_t NV = a.cnt_nv, NS = a.cnt_ns;
-  const uint32_t kCap = 128u * NV + 32u * NS;
-  const int lane = threadIdx.x & 31;
-  const bool w0 = threadIdx.x < 32;
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
-  float* stage = reinterpret_cast<float*>(smem + 16);
-  const uint32_t stage_s = fm_smem_u32(stage), base_s = stage_s + kPairCurPad * 4u;
-  const uint32_t search_s = stage_s + (kPairCurPad + a.base_cap + kPairTailPad) * 4u;
-  const uint32_t final_s = search_s + kSearchBytes;
-  PairXchg* xchg = reinterpret_cast<PairXchg*>(smem + 16 + (kPairCurPad + a.base_cap + kPairTailPad) * 4u +
-                                               kSearchBytes + kFinalBytes);
-  const uint32_t tbl_s = final_s + kFinalBytes + kXchgBytes;
-  const uint32_t m_slots = a.log_m, c_off = 4u * a.log_m;
-  const fm_global_params& g = a.P->g;
-  // my rows of the baseline: warp 0 the first nv0 vector rows, warp 1 the others and the scalar rows
-  const uint32_t nv0 = (NV + 1u) >> 1;
-  const uint32_t r0 = w0 ? 0u : nv0, r1 = w0 ? nv0 : NV;
-  const uint32_t list0 = (w0 ? stage_s : base_s + 512u * nv0) + 4u * (uint32_t)lane;
-
-  if (threadIdx.x == 0) { fm_mbar_init(bar, 1); fm_fence_mbar_init(); }
-  __syncthreads();
-
-  uint64_t s = blockIdx.x;
-  uint32_t phase = 0;
-  if (s < a.n_series && threadIdx.x == 0)
-    issue_rows_pair(a, stage, bar, s, row_len(a.cur_len, s, a.n_cur), row_len(a.base_len, s, a.n_base));
-
-  for (; s < a.n_series; s += gridDim.x) {
-    const uint32_t nc = row_len(a.cur_len, s, a.n_cur);
-    const uint32_t nb = row_len(a.base_len, s, a.n_base);
-    const uint64_t sn = s + gridDim.x;
-    if (sn < a.n_series) {     // pull the next rows into L2 while this series is ranked
-      const uint32_t nbn = row_len(a.base_len, sn, a.n_base);
-      const char* pb = reinterpret_cast<const char*>(a.base + sn * a.base_pitch);
-      for (uint32_t o = threadIdx.x * 128u; o < nbn * 4u; o += 8192u) fm_prefetch_l2(pb + o);
-      if (threadIdx.x < 2) fm_prefetch_l2(reinterpret_cast<const char*>(a.cur + sn * a.cur_pitch) + threadIdx.x * 128);
-    }
-    fm_mbar_wait(bar, phase);
-    phase ^= 1u;
-
-    const bool pair = g.pairwise_mode != FM_PW_NONE && nc > 0 && nb > 0;
-    const bool want_mw = pair && fm_mode_has(g.pairwise_mode, FM_PW_MANN_WHITE) && nc >= g.min_mw && nb >= g.min_mw;
-    const bool want_kw = pair && fm_mode_has(g.pairwise_mode, FM_PW_KRUSKAL) && nc >= g.min_kw && nb >= g.min_kw;
-    const bool want_wx = pair && fm_mode_has(g.pairwise_mode, FM_PW_WILCOXON);
-    const bool ranks = want_mw || want_kw;
-    const bool fuse_model = (a.hist == nullptr) && g.ma_mode == FM_MA_ALL;
-
-    const bool va = (uint32_t)lane < nc, vb = (uint32_t)lane + 32u < nc;
-    const float craw_a = va ? fm_lds_f32(stage_s + 4u * lane) : 0.0f;
-    const float craw_b = vb ? fm_lds_f32(stage_s + 4u * (lane + 32u)) : 0.0f;
-    const float ca = va ? craw_a + 0.0f : CUDART_INF_F;
-    const float cb = vb ? craw_b + 0.0f : CUDART_INF_F;
-    const uint32_t hka = va ? __float_as_uint(ca) : kNoKey, hkb = vb ? __float_as_uint(cb) : kNoKey;
-    const uint32_t mult0 = mult_of(0);
-    const float nokey = __uint_as_float(kNoKey);
-
-    // ---- role phase: warp 0 sorts the current row, warp 1 runs Wilcoxon and the separate models ----
-    WxInts wx = {0u, 0u, 0u, 0u, false};
-    ModelOut mo = {0.0, 0.0, false};
-    if (w0) {
-      if (ranks) {
-        float sa = ca, sb = cb;
-        sort64(sa, sb, lane);
-        const float qa = __shfl_up_sync(FM_FULL, sa, 1);
-        const float last_a = __shfl_sync(FM_FULL, sa, 31);
-        float qb = __shfl_up_sync(FM_FULL, sb, 1);
-        if (lane == 0) qb = last_a;
-        const uint32_t ba = __ballot_sync(FM_FULL, lane == 0 || qa != sa), bb = __ballot_sync(FM_FULL, qb != sb);
-        uint32_t lo_a, e_a, lo_b, e_b;
-        runs_from_ballots(ba, bb, lane, lo_a, e_a, lo_b, e_b);
-        const uint32_t rl_a = min(e_a, nc) - min(lo_a, nc), rl_b = min(e_b, nc) - min(lo_b, nc);
-        fm_sts_f32(search_s + 4u * lane, sa);
-        fm_sts_f32(search_s + 4u * (lane + 33u), sb);
-        sts_v2(final_s + 8u * lane, __float_as_uint(sa), (rl_a << 16) | (2u * lane));
-        sts_v2(final_s + 8u * (lane + 33u), __float_as_uint(sb), (rl_b << 16) | (2u * (lane + 32u)));
-      }
-    } else {
-      if (want_wx) wx = wilcoxon_ints(g, wilcoxon_load(g, stage_s, nc, nb, lane, kPairCurPad), lane);
-      if (a.hist) mo = model_call(&g, a.hist + s * a.hist_pitch, row_len(a.hist_len, s, a.n_hist), true, lane);
-      else if (!fuse_model) mo = model_call(&g, stage + kPairCurPad, nb, false, lane);
-    }
-
-    // ---- sweep 1 over my rows: moments, election pass A --------------------------------------------
-    const double pivot = nb ? (double)fm_lds_f32(base_s) : 0.0;
-    FmMom mom = {0.0, 0.0};
-    const uint32_t nfull = min(r1, max(r0, nb >> 7));        // my rows in [r0, nfull) have no missing point
-    if (ranks) {
-      for (uint32_t o = threadIdx.x * 16u; o < c_off; o += 1024u) sts_zero16(tbl_s + c_off + o);
-      if (!w0) {
-        fm_sts_u32(tbl_s + slot_of(hka, mult0, m_slots), hka);
-        fm_sts_u32(tbl_s + slot_of(hkb, mult0, m_slots), hkb);
-      }
-    }
-    if (ranks || fuse_model) {
-#pragma unroll 1
-      for (uint32_t c = r0; c < nfull; ++c) {
-        const float4 q = fm_lds_v4(base_s + (((uint32_t)lane + 32u * c) << 4));
-        if (fuse_model) {
-          fm_mom_add(mom, q.x, pivot); fm_mom_add(mom, q.y, pivot);
-          fm_mom_add(mom, q.z, pivot); fm_mom_add(mom, q.w, pivot);
-        }
-        if (ranks) {
-          const uint32_t k0 = __float_as_uint(q.x + 0.0f), k1 = __float_as_uint(q.y + 0.0f),
-                         k2 = __float_as_uint(q.z + 0.0f), k3 = __float_as_uint(q.w + 0.0f);
-          fm_sts_u32(tbl_s + slot_of(k0, mult0, m_slots), k0);
-          fm_sts_u32(tbl_s + slot_of(k1, mult0, m_slots), k1);
-          fm_sts_u32(tbl_s + slot_of(k2, mult0, m_slots), k2);
-          fm_sts_u32(tbl_s + slot_of(k3, mult0, m_slots), k3);
-        }
-      }
-#pragma unroll 1
-      for (uint32_t c = nfull; c < r1; ++c) {
-        float k[4];
-        float4 q;
-        const uint32_t e0 = keys4(base_s, c, lane, nb, nokey, k, q);
-        if (fuse_model) {
-          if (e0 < nb) fm_mom_add(mom, q.x, pivot);
-          if (e0 + 1u < nb) fm_mom_add(mom, q.y, pivot);
-          if (e0 + 2u < nb) fm_mom_add(mom, q.z, pivot);
-          if (e0 + 3u < nb) fm_mom_add(mom, q.w, pivot);
-        }
-        if (ranks) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) fm_sts_u32(tbl_s + slot_of(__float_as_uint(k[i]), mult0, m_slots), __float_as_uint(k[i]));
-        }
-      }
-      if (!w0) {
-#pragma unroll 1
-        for (uint32_t j = 0; j < NS; ++j) {
-          const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
-          float v = nokey;
-          if (e < nb) {
-            const float q = fm_lds_f32(base_s + (e << 2));
-            v = q + 0.0f;
-            if (fuse_model) fm_mom_add(mom, q, pivot);
-          }
-          if (ranks) fm_sts_u32(tbl_s + slot_of(__float_as_uint(v), mult0, m_slots), __float_as_uint(v));
-        }
-      }
-    }
-    __syncthreads();                                         // pass A, counters and search tables complete
-
-    // ---- sweep 2 over my rows, overflow rounds ----------------------------------------------------------
-    Tie tie = {0u, 0u};
-    uint32_t acc_all = 0, acc_eq = 0;
-    unsigned long long t_extra = 0;
-    if (ranks) {
-      const float c31 = fm_lds_f32(search_s + 124u);
-      const uint32_t final_k = final_s - 2u * search_s;
-      uint32_t lptr = list0;
-      uint32_t c = r0;
-#pragma unroll 1
-      for (; c + 2u <= nfull; c += 2u) {
-        const float4 q0 = fm_lds_v4(base_s + (((uint32_t)lane + 32u * c) << 4));
-        const float4 q1 = fm_lds_v4(base_s + (((uint32_t)lane + 32u * c + 32u) << 4));
-        const float k[8] = {q0.x + 0.0f, q0.y + 0.0f, q0.z + 0.0f, q0.w + 0.0f,
-                            q1.x + 0.0f, q1.y + 0.0f, q1.z + 0.0f, q1.w + 0.0f};
-        rank_group<8>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
-      }
-#pragma unroll 1
-      for (; c < r1; ++c) {
-        float k[4];
-        float4 q;
-        keys4(base_s, c, lane, nb, nokey, k, q);
-        rank_group<4>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
-      }
-      if (!w0) {
-#pragma unroll 1
-        for (uint32_t j = 0; j < NS; ++j) {
-          const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
-          const float k = e < nb ? fm_lds_f32(base_s + (e << 2)) + 0.0f : nokey;
-          rank_group<1>(&k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
-        }
-        const uint32_t ck[2] = {hka, hkb};                     // the current points last: their list rows are the tail pad
-        classify<2>(ck, tbl_s, c_off, mult0, m_slots, tie, lptr);
-      }
-
-      uint32_t n_l = (lptr - list0) >> 7;
-      for (uint32_t round = 1;; ++round) {
-        if (!__syncthreads_or(n_l > 0u)) break;                // also: everybody's previous pass B is complete
-        if (round == kMaxRounds) {
-          // Not reached in practice.  What is left are whole classes: count each key's class directly.
-          fm_sts_u32(final_s + 4u * threadIdx.x, n_l);
-          fm_sts_u32(final_s + 256u + 4u * threadIdx.x, list0);
-          __syncthreads();
-          for (uint32_t k = 0; k < n_l; ++k) {
-            const uint32_t mine = fm_lds_u32(list0 + 128u * k);
-            uint32_t t = 0;
-            for (uint32_t l2 = 0; l2 < 64u; ++l2) {
-              const uint32_t n2 = fm_lds_u32(final_s + 4u * l2), b2 = fm_lds_u32(final_s + 256u + 4u * l2);
-              for (uint32_t k2 = 0; k2 < n2; ++k2) t += fm_lds_u32(b2 + 128u * k2) == mine;
-            }
-            t_extra += (unsigned long long)t * t - 1ull;
-          }
-          break;
-        }
-        for (uint32_t o = threadIdx.x * 16u; o < c_off; o += 1024u) sts_zero16(tbl_s + c_off + o);
-        const uint32_t mult = mult_of(round);
-        {
-          uint32_t k = 0;
-          for (; k + 4u <= n_l; k += 4u) {
-            uint32_t bits[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) bits[i] = fm_lds_u32(list0 + 128u * (k + i));
-#pragma unroll
-            for (int i = 0; i < 4; ++i) fm_sts_u32(tbl_s + slot_of(bits[i], mult, m_slots), bits[i]);
-          }
-          for (; k < n_l; ++k) {
-            const uint32_t bits = fm_lds_u32(list0 + 128u * k);
-            fm_sts_u32(tbl_s + slot_of(bits, mult, m_slots), bits);
-          }
-        }
-        __syncthreads();
-        uint32_t wptr = list0;
-        {
-          uint32_t k = 0;
-          for (; k + 4u <= n_l; k += 4u) {
-            uint32_t bits[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) bits[i] = fm_lds_u32(list0 + 128u * (k + i));
-            classify<4>(bits, tbl_s, c_off, mult, m_slots, tie, wptr);
-          }
-          for (; k < n_l; ++k) {
-            const uint32_t bits = fm_lds_u32(list0 + 128u * k);
-            classify<1>(&bits, tbl_s, c_off, mult, m_slots, tie, wptr);
-          }
-        }
-        n_l = (wptr - list0) >> 7;
-      }
-    }
-
-    // ---- partial sums; warp 1 hands its own over -------------------------------------------------------
-    uint32_t sum_lu = 0;
-    unsigned long long t3 = 0, tx = 0;
-    if (ranks) {
-      sum_lu = __reduce_add_sync(FM_FULL, (acc_all & 0xFFFFu) + (acc_eq >> 16));
-      const uint32_t tl = tie.sq + (0u - tie.lin);
-      t3 = (unsigned long long)__reduce_add_sync(FM_FULL, tl & 0xFFFFu) +
-           ((unsigned long long)__reduce_add_sync(FM_FULL, tl >> 16) << 16);
-      tx = (unsigned long long)fm_warp_sum((long long)t_extra);
-    }
-    double s1 = 0.0, s2 = 0.0;
-    if (fuse_model) { s1 = fm_warp_sum(mom.s1); s2 = fm_warp_sum(mom.s2); }
-    if (!w0 && lane == 0) {
-      xchg->s1 = s1; xchg->s2 = s2; xchg->mean = mo.mean; xchg->sigma = mo.sigma;
-      xchg->t3 = t3; xchg->t_extra = tx; xchg->sum_lu = sum_lu;
-      xchg->np = wx.np; xchg->wp2 = wx.wp2; xchg->wm2 = wx.wm2; xchg->twx = wx.t;
-      xchg->flags = (wx.run ? 1u : 0u) | (mo.ok ? 2u : 0u);
-    }
-    __syncthreads();                                         // hand-over visible; nobody reads the stage any more
-    if (sn < a.n_series && threadIdx.x == 0) {
-      fm_fence_proxy_async();
-      issue_rows_pair(a, stage, bar, sn, row_len(a.cur_len, sn, a.n_cur), row_len(a.base_len, sn, a.n_base));
-    }
-    if (!w0) continue;                                       // warp 1 goes on to the next series
-
-    // ---- warp 0: a5..a9 -----------------------------------------------------------------------------------
-    const PairXchg x1 = *xchg;
-    const uint32_t ty = a.metric_type ? a.metric_type[s] : 0u;
-    const fm_type_params tp = a.P->types[ty < a.P->n_types ? ty : 0u];
-    fm_series_rec rec;
-    fm_rec_init(rec);
-    fm_rank_aux ax = {0, 0, 0, 0, 0, 0u, 0u};
-    uint32_t status = 0;
-    if (nc == 0) status |= FM_ST_NO_CURRENT;
-    wx.np = x1.np; wx.wp2 = x1.wp2; wx.wm2 = x1.wm2; wx.t = x1.twx; wx.run = (x1.flags & 1u) != 0;
-    ax.n_wx = wx.np;
-    bool model_ok;
-    if (fuse_model) {
-      model_ok = nb >= max(g.min_hist_points, g.ddof + 1u);
-      s1 += x1.s1; s2 += x1.s2;
-    } else {
-      model_ok = (x1.flags & 2u) != 0;
-      rec.mean = x1.mean; rec.sigma = x1.sigma;
-    }
-    if (!model_ok) status |= FM_ST_HIST_INSUFFICIENT;
-    long long r2c = 0, Tt = 0;
-    if (ranks) {
-      r2c = (long long)nc * (nc + 1) + 2ll * nc * nb - (long long)(sum_lu + x1.sum_lu);
-      const unsigned long long ninv = (unsigned long long)(kCap - nb) + (64u - nc);
-      Tt = (long long)(3ull * (t3 + x1.t3) + tx + x1.t_extra - (ninv * ninv * ninv - ninv));
-      ax.r2_cur = r2c; ax.t_mw = Tt;
-    }
-    finish_stats(a, g, tp, s, lane, nc, nb, pair, want_mw, want_kw, wx, fuse_model, model_ok, s1, s2, pivot, r2c, Tt,
-                 craw_a, craw_b, va, vb, rec, ax, status);
-  }
-}
-
 }  // namespace
 
 // tiers (vector rows, scalar rows) -> capacity 128 NV + 32 NS baseline points.  The rows are walked
@@ -969,10 +632,7 @@ __global__ void __launch_bounds__(64, 14) k_canary_pair(const FmKArgs a) {
 #define FM_COUNT_TIERS(X) X(1, 0) X(2, 0) X(4, 0) X(8, 0) X(11, 1) X(12, 0) X(16, 0)
 
 cudaError_t fm_canary_count_smem_attr(int bytes) {
-  cudaError_t e = cudaFuncSetAttribute(k_canary_count<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_canary_count<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_canary_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  return e;
+  return cudaFuncSetAttribute(k_canary_count, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
 // smallest tier that holds n_base points; 0 if none does
@@ -984,20 +644,8 @@ uint32_t fm_canary_count_tier(uint32_t n_base, int* nv, int* ns) {
 }
 
 size_t fm_canary_count_fixed_bytes() { return 16 + kSearchBytes + kFinalBytes; }
-// two warps per series: bytes per CTA beside the baseline capacity and the election table
-size_t fm_canary_pair_fixed_bytes() {
-  return 16 + (size_t)(kPairCurPad + kPairTailPad) * 4 + kSearchBytes + kFinalBytes + kXchgBytes;
-}
-
 int fm_launch_canary_count(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st) {
   const size_t smem = (size_t)warps_per_cta * a.warp_bytes;
-  if (a.cnt_nv == 11u) k_canary_count<11><<<grid, warps_per_cta * 32, smem, st>>>(a);
-  else k_canary_count<0><<<grid, warps_per_cta * 32, smem, st>>>(a);
-  return 1;
-}
-
-// a.warp_bytes = bytes of shared memory per CTA (= per series in flight)
-int fm_launch_canary_pair(const FmKArgs& a, int grid, cudaStream_t st) {
-  k_canary_pair<<<grid, 64, a.warp_bytes, st>>>(a);
+  k_canary_count<<<grid, warps_per_cta * 32, smem, st>>>(a);
   return 1;
 }

@@ -16,12 +16,11 @@ from parity import assert_records_match, bound_masks
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module", params=["auto", "auto-tiny", "count1", "count1-tiny", "sort", "generic", "elect", "elect-1stage"])
+@pytest.fixture(scope="module", params=["auto", "auto-tiny", "auto-1stage", "sort", "generic", "elect", "elect-1stage"])
 def ctx(request):
-    """auto: the counting canary kernel with two warps per series (k_canary_pair, fm_canary_count.cu)
-    wherever it applies; count1: its one-warp-per-series form (k_canary_count); -tiny: the same with
-    an election table of 64 slots, so that every series goes through all the overflow rounds and the
-    direct count behind them; sort: the register-sort canary kernel (fm_canary_sort.cu); elect:
+    """auto: the counting canary kernel (fm_canary_count.cu) wherever it applies; auto-tiny: the same
+    with an election table of 64 slots, so that every series goes through all the overflow rounds and
+    the direct count behind them; auto-1stage: its free-running launch shape (no barrier per series); sort: the register-sort canary kernel (fm_canary_sort.cu); elect:
     the CTA-per-series election kernel (fm_canary_elect.cu); generic: the shared-memory sort kernel
     for everything (the FOREMAST_CUDA_* switches are read when the ctx is created)."""
     import os
@@ -30,6 +29,7 @@ def ctx(request):
     os.environ["FOREMAST_CUDA_STAGES"] = "1" if request.param.endswith("1stage") else "0"
     if request.param.endswith("tiny"):
         os.environ["FOREMAST_CUDA_SLOTS"] = "64"
+        os.environ["FOREMAST_CUDA_STAGES"] = "0"
     c = Context(0)
     for k in ("FOREMAST_CUDA_PATH", "FOREMAST_CUDA_STAGES", "FOREMAST_CUDA_SLOTS"):
         os.environ.pop(k, None)
