@@ -60,7 +60,7 @@ class ClockSampler(threading.Thread):
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
                  "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
-                self.rows.append([x.strip() for x in line.split(",")])
+                self.rows.append([time.perf_counter()] + [x.strip() for x in line.split(",")])
         except Exception:
             pass
 
@@ -68,9 +68,16 @@ class ClockSampler(threading.Thread):
         if self.proc is not None:
             self.proc.terminate()
         self.join(timeout=2)
+        return self.window()
+
+    def window(self, t0=None, t1=None):
+        """Clock record of the samples that arrived in [t0, t1] (all of them by default); a window
+        shorter than the sampling period falls back to the samples around it."""
+        rows = [r for r in self.rows if (t0 is None or r[0] >= t0 - 0.15) and (t1 is None or r[0] <= t1 + 0.15)]
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for r in rows:
+            r = r[1:]
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
                 for n, v in zip(names, r[3:7]):
@@ -96,8 +103,14 @@ def measured_traffic(kernel, workload, n_series):
     """DRAM bytes of one launch from the committed ncu capture of that kernel ON THAT WORKLOAD
     (None if this combination was not captured)."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r01", "traffic.json")) as f:
-            t = json.load(f).get(kernel, {}).get(workload)
+        t = None
+        for rnd in ("r02", "r01"):
+            path = os.path.join(ROOT, "profiles", rnd, "traffic.json")
+            if os.path.exists(path):
+                with open(path) as f:
+                    t = json.load(f).get(kernel, {}).get(workload)
+            if t is not None:
+                break
         if t is None:
             return None
         return int(t["bytes_per_series"]) * int(n_series)
@@ -171,6 +184,172 @@ def run_reference(args, w, rank):
     print(json.dumps(line), flush=True)
 
 
+def canary_kernel_name(n_cur, n_base):
+    """Which kernel plan_score (csrc/fm_api.cu) picks for a canary batch of this shape."""
+    if n_cur <= 63 and n_base <= 2048:
+        return "k_canary_count"
+    if n_cur <= 64 and n_base <= 2048:
+        r = 16 if n_base <= 512 else 32 if n_base <= 1024 else 64
+        return "k_canary_sort<%d, %d>" % (r, 3 * r // 4 if n_base <= 24 * r else r)
+    return "k_score_series"
+
+
+def secondary(ctx, sampler, peak, steps=5, warmup=3):
+    """The other BASELINE.json configs under the same clock sampler as the headline (device-resident
+    rows, CUDA events on the library stream, inputs larger than L2): config 2 (10k series, 10080-point
+    history; and read literally, Mann-Whitney against a 10080-point baseline), config 4 (100k services
+    through fm_score_groups_device) and config 5 (MA-only, 1M series, four window lengths, WITH the
+    series -> API -> service roll-up: 4 metrics x 8 APIs per service)."""
+    import ctypes as C
+    import numpy as np
+    from foremast_1_b200 import _abi as A
+    from foremast_1_b200.engine import synth_desc
+    out = {}
+    g0, table = A.default_params()
+
+    def timed(run, t):
+        for _ in range(warmup):
+            run()
+        ctx.sync()
+        t0 = time.perf_counter()
+        ms = []
+        for _ in range(steps):
+            run()
+            ms.append(t.main_kernel_ms)
+        ctx.sync()
+        return statistics.median(ms), sampler.window(t0, time.perf_counter())
+
+    def series_case(name, config, S, n_cur, n_base, n_hist, mode, canary, compact, rollup):
+        g, _ = A.default_params()
+        g.pairwise_mode = getattr(A, "FM_PW_" + mode)
+        ctx.set_params(g, table)
+        d = synth_desc(config, S, n_cur, n_base, n_hist)
+        ptrs = [ctx.dev_alloc(S * d.cur_pitch * 4), ctx.dev_alloc(S * d.base_pitch * 4) if n_base else None,
+                ctx.dev_alloc(S * d.hist_pitch * 4) if n_hist else None, ctx.dev_alloc(S)]
+        rdt = A.COMPACT_REC if compact else A.SERIES_REC
+        d_out = ctx.dev_alloc(S * rdt.itemsize)
+        ctx.synth_device(d, *ptrs)
+        b = A.Batch()
+        b.struct_size = C.sizeof(A.Batch)
+        b.strategy = A.FM_STRAT_CANARY if canary else A.FM_STRAT_HISTORICAL
+        b.n_series = S
+        b.cur, b.n_cur, b.cur_pitch = ptrs[0], n_cur, d.cur_pitch
+        if n_base:
+            b.base, b.n_base, b.base_pitch = ptrs[1], n_base, d.base_pitch
+        if n_hist:
+            b.hist, b.n_hist, b.hist_pitch = ptrs[2], n_hist, d.hist_pitch
+        b.metric_type = ptrs[3]
+        b.record_kind = A.FM_REC_COMPACT if compact else A.FM_REC_FULL
+        extra = []
+        d_api = d_svc = None
+        if rollup:
+            api = (np.arange(S) // 4).astype(np.uint32)
+            svc = (np.arange(S // 4) // 8).astype(np.uint32)
+            p_api, p_svc = ctx.dev_alloc(api.nbytes), ctx.dev_alloc(svc.nbytes)
+            ctx.h2d(p_api, api); ctx.h2d(p_svc, svc)
+            b.api_id, b.api_service, b.n_apis, b.n_services = p_api, p_svc, S // 4, S // 32
+            d_api, d_svc = ctx.dev_alloc(S // 4 * 16), ctx.dev_alloc(S // 32 * 16)
+            extra = [p_api, p_svc, d_api, d_svc]
+        t = A.Timing()
+        ms, clk = timed(lambda: ctx.score_device(b, d_out, None, d_api, d_svc, timing=t), t)
+        bps = 4 * (n_cur + n_base + n_hist) + rdt.itemsize
+        res = {"series": S, "n_cur": n_cur, "n_base": n_base, "n_hist": n_hist, "pairwise": mode,
+               "kernel": canary_kernel_name(n_cur, n_base) if canary else
+               "k_ma_only<%d>" % (16 if n_hist >= 1200 else 8 if n_hist >= 200 else 4),
+               "ms": ms, "series_per_s": S / (ms / 1e3), "bytes_per_series": bps,
+               "achieved_GBps": S * bps / (ms / 1e3) / 1e9, "frac": S * bps / (ms / 1e3) / 1e9 / peak,
+               "launches_per_step": int(t.launches), "clocks": clk}
+        if rollup:
+            sv = np.zeros(S // 32, A.ROLLUP_REC)
+            ctx.d2h(sv, d_svc)
+            res["rollup"] = {"apis": S // 4, "services": S // 32,
+                             "service_severity_histogram": np.bincount(sv["severity"], minlength=3).tolist()}
+        for q in ptrs + [d_out] + extra:
+            ctx.dev_free(q)
+        out[name] = res
+
+    series_case("c2", 2, 10_000, 60, 1440, 10080, "MANN_WHITE", True, False, False)
+    series_case("c2_base10080", 2, 10_000, 60, 10080, 0, "MANN_WHITE", True, False, False)
+    for nh in (60, 240, 1440, 10080):
+        series_case("c5_%d" % nh, 5, 1_000_000, 60, 0, nh, "NONE", False, True, True)
+
+    # config 4: 100k services x 3..8 pod groups x 60 integer counts, Kruskal-Wallis + per-group bounds
+    V = 100_000
+    rng = np.random.default_rng(44)
+    K = rng.integers(3, 9, V)
+    off = np.concatenate([[0], np.cumsum(K)]).astype(np.uint32)
+    G = int(off[-1])
+    svc_of = np.repeat(np.arange(V, dtype=np.uint64), K)
+    ids = (svc_of << np.uint64(4)) + (np.arange(G, dtype=np.uint64) - off[:-1].astype(np.uint64)[svc_of.astype(np.int64)])
+    hids = np.arange(V, dtype=np.uint64) << np.uint64(4)
+    g, _ = A.default_params()
+    g.pairwise_mode = A.FM_PW_KRUSKAL
+    ctx.set_params(g, table)
+    d_ids, d_hids = ctx.dev_alloc(ids.nbytes), ctx.dev_alloc(hids.nbytes)
+    ctx.h2d(d_ids, ids); ctx.h2d(d_hids, hids)
+    dg = synth_desc(4, G, 60, 0, 0, row_ids=d_ids)
+    dh = synth_desc(4, V, 60, 0, 1440, row_ids=d_hids)
+    d_cur, d_hist, d_mt = ctx.dev_alloc(G * dg.cur_pitch * 4), ctx.dev_alloc(V * dh.hist_pitch * 4), ctx.dev_alloc(V)
+    ctx.synth_device(dg, d_cur, None, None, None)
+    ctx.synth_device(dh, None, None, d_hist, d_mt)
+    d_off = ctx.dev_alloc(off.nbytes); ctx.h2d(d_off, off)
+    gb = A.GroupBatch()
+    gb.struct_size = C.sizeof(A.GroupBatch)
+    gb.n_services, gb.n_groups, gb.group_offsets = V, G, d_off
+    gb.cur, gb.n_cur, gb.cur_pitch = d_cur, 60, dg.cur_pitch
+    gb.hist, gb.n_hist, gb.hist_pitch = d_hist, 1440, dh.hist_pitch
+    gb.metric_type = d_mt
+    d_out, d_svc = ctx.dev_alloc(G * 96), ctx.dev_alloc(V * 16)
+    t = A.Timing()
+    ms, clk = timed(lambda: ctx.score_groups_device(gb, d_out, d_svc, t), t)
+    bytes_alg = 4 * (G * 60 + V * 1440) + G * 96 + V * 16
+    out["c4"] = {"services": V, "groups": G, "kernel": "k_groups_sort + k_score_groups (deferred list)", "ms": ms,
+                 "services_per_s": V / (ms / 1e3), "bytes_per_service": bytes_alg / V,
+                 "achieved_GBps": bytes_alg / (ms / 1e3) / 1e9, "frac": bytes_alg / (ms / 1e3) / 1e9 / peak,
+                 "launches_per_step": int(t.launches), "clocks": clk}
+    # config 4 end to end: pinned host rows through fm_score_groups
+    try:
+        from foremast_1_b200.engine import Pinned
+        from foremast_1_b200 import _ffi
+        p_cur = Pinned((G, dg.cur_pitch), np.float32)
+        p_hist = Pinned((V, dh.hist_pitch), np.float32)
+        p_mt = Pinned((V,), np.uint8)
+        p_off = Pinned((V + 1,), np.uint32)
+        p_rec = Pinned((G,), A.SERIES_REC)
+        p_svc = Pinned((V,), A.ROLLUP_REC)
+        p_off.array[:] = off
+        hg = synth_desc(4, G, 60, 0, 0, row_ids=ids.ctypes.data)
+        hh = synth_desc(4, V, 60, 0, 1440, row_ids=hids.ctypes.data)
+        lib = _ffi.lib()
+        assert lib.fm_synth_fill_host(C.byref(hg), p_cur.ptr, None, None, None, 0) == 0
+        assert lib.fm_synth_fill_host(C.byref(hh), None, None, p_hist.ptr, p_mt.ptr, 0) == 0
+        hb = A.GroupBatch()
+        hb.struct_size = C.sizeof(A.GroupBatch)
+        hb.n_services, hb.n_groups, hb.group_offsets = V, G, p_off.ptr
+        hb.cur, hb.n_cur, hb.cur_pitch = p_cur.ptr, 60, dg.cur_pitch
+        hb.hist, hb.n_hist, hb.hist_pitch = p_hist.ptr, 1440, dh.hist_pitch
+        hb.metric_type = p_mt.ptr
+        te = A.Timing()
+
+        def e2e_run():
+            _ffi.check(lib.fm_score_groups(ctx._h, C.byref(hb), C.c_void_p(p_rec.ptr), C.c_void_p(p_svc.ptr), C.byref(te)), ctx._h)
+        e2e_run()
+        w0 = time.perf_counter()
+        for _ in range(3):
+            e2e_run()
+        e_s = (time.perf_counter() - w0) / 3
+        out["c4"]["e2e"] = {"services_per_s": V / e_s, "ms_per_step": 1e3 * e_s, "h2d_bytes_per_step": int(te.h2d_bytes),
+                            "d2h_bytes_per_step": int(te.d2h_bytes), "launches_per_step": int(te.launches)}
+        for pb in (p_cur, p_hist, p_mt, p_off, p_rec, p_svc):
+            pb.free()
+    except Exception as e:  # the device-resident numbers stand on their own
+        out["c4"]["e2e"] = {"error": f"{type(e).__name__}: {e}"}
+    for q in (d_ids, d_hids, d_cur, d_hist, d_mt, d_off, d_out, d_svc):
+        ctx.dev_free(q)
+    ctx.set_params(g0, table)
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -183,6 +362,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the config 2 / 4 / 5 block")
     ap.add_argument("--mode", default="", help="override the workload's pairwise mode (diagnostics only)")
     ap.add_argument("--n-hist", type=int, default=-1, help="override the history length (config 5 sweep)")
     ap.add_argument("--compact", action="store_true", help="16-byte records (config 5 sweep)")
@@ -338,14 +518,26 @@ def main():
             if pbuf:
                 pbuf.free()
 
+    sec = None
+    if world == 1 and not args.no_secondary and args.workload == "c3" and args.n_hist < 0 and not args.mode:
+        for q in (d_cur, d_base, d_hist, d_mt, d_out):
+            if q:
+                ctx.dev_free(q)
+        s2 = ClockSampler(local)
+        s2.start()
+        time.sleep(0.3)
+        try:
+            sec = secondary(ctx, s2, measured_peak()[0])
+        except Exception as e:  # the headline stands on its own
+            sec = {"error": f"{type(e).__name__}: {e}"}
+        s2.stop()
+
     if rank == 0:
         peak, peak_src = measured_peak()
         rec_bytes = rec_dtype.itemsize
         bps = algorithmic_bytes(w, rec_bytes)
         achieved = S * bps / (main_ms_max / args.steps / 1e3) / 1e9
-        sort_r = 16 if w["n_base"] <= 512 else 32 if w["n_base"] <= 1024 else 64
-        kernel = (("k_canary_sort<%d, %d>" % (sort_r, 3 * sort_r // 4 if w["n_base"] <= 24 * sort_r else sort_r))
-                  if (w["canary"] and w["n_cur"] <= 64 and w["n_base"] <= 2048) else
+        kernel = (canary_kernel_name(w["n_cur"], w["n_base"]) if w["canary"] else
                   ("k_ma_only<%d>" % (16 if w["n_hist"] >= 1200 else 8 if w["n_hist"] >= 200 else 4)))
         traffic = measured_traffic(kernel, args.workload, S) if (args.n_hist < 0 and not args.mode) else None
         line = {
@@ -370,6 +562,8 @@ def main():
         }
         if e2e is not None:
             line["e2e"] = e2e
+        if sec is not None:
+            line["secondary"] = sec
         if world == 1 and not args.no_cpu:
             cb, _, _ = cpu_baseline(w)
             line["cpu_baseline"] = cb

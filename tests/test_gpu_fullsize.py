@@ -103,12 +103,19 @@ def test_config3_one_million_series():
         from make_golden_shim import host_batch
         ora = O.score_batch(g, t, host_batch(A.FM_STRAT_CANARY, cur, base, None, mt), n_threads=8)
         k = ids.astype(np.int64)
-        assert_records_match(rec[k], ora["rec"], cur[:, :nc], None, bound_masks(t, mt, ids.size), aux[k], ora["aux"])
+        assert_records_match(rec[k], ora["rec"], cur[:, :nc], None, bound_masks(t, mt, ids.size), aux[k], ora["aux"],
+                             alpha=g.alpha)
         free_all(ctx, p)
 
 
 def test_config5_ma_sweep_and_rollup():
+    """Config 5 at size: MA-only bounds over three window lengths WITH the series -> API -> service
+    roll-up (4 metrics per API, 8 APIs per service: 250 000 APIs, 31 250 services).  Conservation laws
+    over the whole batch, and a strided sample of whole services against the oracle: series records,
+    API records and service records."""
     S = 1_000_000
+    api = (np.arange(S) // 4).astype(np.uint32)
+    svc = (np.arange(S // 4) // 8).astype(np.uint32)
     with Context(0) as ctx:
         g, t = A.default_params()
         ctx.set_params(g, t)
@@ -116,19 +123,40 @@ def test_config5_ma_sweep_and_rollup():
             d = synth_desc(5, S, 60, 0, nh)
             b, p = device_batch(ctx, d, A.FM_STRAT_HISTORICAL)
             b.record_kind = A.FM_REC_COMPACT
+            p["api"], p["svc"] = ctx.dev_alloc(api.nbytes), ctx.dev_alloc(svc.nbytes)
+            ctx.h2d(p["api"], api); ctx.h2d(p["svc"], svc)
+            b.api_id, b.api_service, b.n_apis, b.n_services = p["api"], p["svc"], S // 4, S // 32
             p["out"] = ctx.dev_alloc(S * 16)
-            ctx.score_device(b, p["out"], timing=A.Timing())
+            p["oapi"], p["osvc"] = ctx.dev_alloc(S // 4 * 16), ctx.dev_alloc(S // 32 * 16)
+            ctx.score_device(b, p["out"], None, p["oapi"], p["osvc"], A.Timing())
             rec = np.zeros(S, A.COMPACT_REC); ctx.d2h(rec, p["out"])
+            rapi = np.zeros(S // 4, A.ROLLUP_REC); ctx.d2h(rapi, p["oapi"])
+            rsvc = np.zeros(S // 32, A.ROLLUP_REC); ctx.d2h(rsvc, p["osvc"])
             assert ((rec["verdict"] == A.FM_UNHEALTHY) == (rec["n_anom"] > 0)).all()
             assert (rec["status"] == 0).all()
-            ids = np.arange(0, S, 7919, dtype=np.uint64)
+            # roll-up conservation: every series counted once, severities follow rule A.9
+            assert (rapi["n_children"] == 4).all() and (rsvc["n_children"] == 8).all()
+            un_api = np.add.reduceat((rec["verdict"] == A.FM_UNHEALTHY).astype(np.int64), np.arange(0, S, 4))
+            assert (rapi["n_unhealthy"] == un_api).all() and (rapi["n_unknown"] == 0).all()
+            assert ((rapi["severity"] == A.FM_UNHEALTHY) == (un_api > 0)).all()
+            un_svc = np.add.reduceat((rapi["severity"] == A.FM_UNHEALTHY).astype(np.int64), np.arange(0, S // 4, 8))
+            assert (rsvc["n_unhealthy"] == un_svc).all()
+            assert ((rsvc["severity"] == A.FM_UNHEALTHY) == (un_svc > 0)).all()
+            assert (rsvc["severity"] == A.FM_UNHEALTHY).any() and (rsvc["severity"] == A.FM_HEALTHY).any()
+            # whole services (32 consecutive series each) against the oracle, roll-up included
+            pick = np.arange(0, S // 32, 251)
+            ids = (pick[:, None] * 32 + np.arange(32)[None, :]).ravel().astype(np.uint64)
             ds = synth_desc(5, ids.size, 60, 0, nh, row_ids=ids.ctypes.data)
             cur, _, hist, mt = synth_host(ds)
             from make_golden_shim import host_batch
             hb = host_batch(A.FM_STRAT_HISTORICAL, cur, None, hist, mt)
             hb.record_kind = A.FM_REC_COMPACT
+            lapi = (np.arange(ids.size) // 4).astype(np.uint32)
+            lsvc = (np.arange(ids.size // 4) // 8).astype(np.uint32)
+            hb.api_id, hb.api_service, hb.n_apis, hb.n_services = lapi.ctypes.data, lsvc.ctypes.data, ids.size // 4, pick.size
             ora = O.score_batch(g, t, hb, n_threads=8, want_aux=False)
-            got = rec[ids.astype(np.int64)]
+            k = ids.astype(np.int64)
+            got = rec[k]
             same = got == ora["rec"]
             # compact records carry no bounds: allow the documented 1e-6 flag tolerance by re-checking
             # disagreeing series with full records
@@ -138,6 +166,12 @@ def test_config5_ma_sweep_and_rollup():
                 fb = host_batch(A.FM_STRAT_HISTORICAL, cur[bad], None, hist[bad], mt[bad])
                 fo = O.score_batch(g, t, fb, n_threads=2)
                 assert_records_match(full["rec"], fo["rec"], cur[bad][:, :60], None, bound_masks(t, mt[bad], bad.size))
+            # roll-up records of the sampled services: exact wherever their series agree exactly
+            svc_ok = same.reshape(pick.size, 32).all(axis=1)
+            api_ok = same.reshape(-1, 4).all(axis=1)
+            gapi = rapi[(pick[:, None] * 8 + np.arange(8)[None, :]).ravel()]
+            assert (gapi[api_ok] == ora["api"][api_ok]).all()
+            assert (rsvc[pick][svc_ok] == ora["svc"][svc_ok]).all() and svc_ok.mean() > 0.99
             free_all(ctx, p)
 
 

@@ -54,7 +54,7 @@ def both(ctx, g, table, cur, base=None, hist=None, **kw):
     cl = kw.get("cur_len")
     listed = assert_records_match(out["rec"], ora["rec"], curm[:, : b.n_cur], cl,
                                   bound_masks(table, kw.get("metric_type"), S),
-                                  out["aux"], ora["aux"])
+                                  out["aux"], ora["aux"], alpha=g.alpha)
     if out["api"] is not None:
         assert (out["api"] == ora["api"]).all()
     if out["svc"] is not None:
