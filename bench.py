@@ -514,6 +514,34 @@ def main():
                "h2d_bytes_per_step": int(te.h2d_bytes), "d2h_bytes_per_step": int(te.d2h_bytes),
                "series_per_step_per_gpu": Se, "steps": args.e2e_steps, "ms_per_step": 1e3 * e_s / args.e2e_steps,
                "launches_per_step": int(launches_e2e), "matches_device_pass": same}
+        # second poll of the same jobs: baselines resident in HBM (fm_score_batch_cached), only the
+        # current rows cross PCIe
+        try:
+            p_ids = Pinned((Se,), np.uint64)
+            p_ids.array[:] = (np.arange(Se, dtype=np.uint64) + np.uint64(rank * S + 1)) * np.uint64(0x9E3779B97F4A7C15)
+            ctx.cache_configure(Se * 4 * (de.base_pitch + de.hist_pitch) + (64 << 20))
+            tw = A.Timing()
+            ctx.score_host(hb, p_out.ptr, timing=tw, row_ids=p_ids.ptr)       # cold: fills the cache
+            cold_same = bool((p_out.array[: rec.size] == rec[: min(rec.size, Se)]).all()) if Se >= rec.size else None
+            ctx.score_host(hb, p_out.ptr, timing=tw, row_ids=p_ids.ptr)       # warm-up of the warm path
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.e2e_steps):
+                ctx.score_host(hb, p_out.ptr, timing=tw, row_ids=p_ids.ptr)
+            barrier()
+            w_s = rank_max(time.perf_counter() - t0)
+            st = ctx.cache_stats()
+            warm_same = bool((p_out.array[: rec.size] == rec[: min(rec.size, Se)]).all()) if Se >= rec.size else None
+            e2e["warm"] = {"value": world * Se * args.e2e_steps / w_s, "unit": "series/s",
+                           "what": "re-poll of the same row ids through fm_score_batch_cached: baselines resident in HBM",
+                           "h2d_bytes_per_step": int(tw.h2d_bytes), "d2h_bytes_per_step": int(tw.d2h_bytes),
+                           "ms_per_step": 1e3 * w_s / args.e2e_steps, "launches_per_step": int(tw.launches),
+                           "kernel_ms_per_step": float(tw.kernel_ms), "resident_rows": st["resident_rows"],
+                           "matches_device_pass": warm_same and cold_same}
+            ctx.cache_configure(0)
+            p_ids.free()
+        except Exception as e:  # the cold number stands on its own
+            e2e["warm"] = {"error": f"{type(e).__name__}: {e}"}
         for pbuf in (p_cur, p_base, p_hist, p_mt, p_out):
             if pbuf:
                 pbuf.free()

@@ -74,6 +74,11 @@ class Timing(C.Structure):
                 ("main_kernel_ms", C.c_float), ("reserved", C.c_uint32)]
 
 
+class CacheStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("max_bytes", "row_bytes", "capacity_rows", "resident_rows",
+                                          "hits", "misses", "evictions", "uncached")]
+
+
 class SynthDesc(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("config", C.c_uint32), ("seed", C.c_uint64),
                 ("first_series", C.c_uint64), ("n_series", C.c_uint64),

@@ -27,6 +27,10 @@ SYMBOLS = {
     "fm_memcpy_h2d": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "fm_memcpy_d2h": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "fm_score_batch": (C.c_int32, [C.c_void_p, C.POINTER(A.Batch), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(A.Timing)]),
+    "fm_score_batch_cached": (C.c_int32, [C.c_void_p, C.POINTER(A.Batch), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(A.Timing)]),
+    "fm_cache_configure": (C.c_int32, [C.c_void_p, C.c_uint64]),
+    "fm_cache_query": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
+    "fm_cache_get_stats": (C.c_int32, [C.c_void_p, C.c_void_p]),
     "fm_score_batch_device": (C.c_int32, [C.c_void_p, C.POINTER(A.Batch), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(A.Timing)]),
     "fm_score_groups": (C.c_int32, [C.c_void_p, C.POINTER(A.GroupBatch), C.c_void_p, C.c_void_p, C.POINTER(A.Timing)]),
     "fm_score_groups_device": (C.c_int32, [C.c_void_p, C.POINTER(A.GroupBatch), C.c_void_p, C.c_void_p, C.POINTER(A.Timing)]),

@@ -7,6 +7,7 @@
 #include <new>
 #include <string>
 #include <thread>
+#include <unordered_map>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -35,6 +36,40 @@ thread_local std::string g_create_error;
 
 }  // namespace
 
+// Device-resident baseline / history rows between calls (MAX_CACHE_SIZE, "max cached model size",
+// foremast-brain/README.md:30).  A job is re-judged on every poll until its endTime
+// (docs/guides/design.md:43) and its baseline and 7-day history do not change in between, so
+// fm_score_batch_cached keeps those rows in HBM under a caller-supplied 64-bit row id and uploads
+// only rows it does not hold (plus every current row).  One layout (n_base, pitch, n_hist, pitch) at
+// a time; a batch of another layout starts the cache afresh.  Slots are recycled least-recently-
+// scored first (a clock hand over the per-slot epoch of the last call that used it).
+struct RowCache {
+  static constexpr uint32_t kNone = 0xFFFFFFFFu;
+  uint64_t max_bytes = 0;
+  uint32_t n_base = 0, base_pitch = 0, n_hist = 0, hist_pitch = 0;
+  uint64_t cap = 0;                         // slots
+  float* d_base = nullptr;                  // [cap x base_pitch]
+  float* d_hist = nullptr;                  // [cap x hist_pitch]
+  std::vector<uint64_t> slot_id;
+  std::vector<uint32_t> slot_epoch, slot_blen, slot_hlen;
+  std::vector<uint8_t> slot_live;
+  std::unordered_map<uint64_t, uint32_t> index;
+  uint64_t n_live = 0, hand = 0;
+  uint32_t epoch = 0;
+  std::vector<uint64_t> prev_ids;           // ids and slots of the previous call: a re-poll of the
+  std::vector<uint32_t> prev_slot;          // same job set resolves without a single hash lookup
+  uint64_t hits = 0, misses = 0, evictions = 0, uncached = 0;
+
+  void release() {
+    if (d_base) cudaFree(d_base);
+    if (d_hist) cudaFree(d_hist);
+    d_base = d_hist = nullptr;
+    cap = 0; n_live = 0; hand = 0;
+    slot_id.clear(); slot_epoch.clear(); slot_blen.clear(); slot_hlen.clear(); slot_live.clear();
+    index.clear(); prev_ids.clear(); prev_slot.clear();
+  }
+};
+
 struct fm_ctx {
   int device = 0;
   int num_sms = 148;
@@ -46,6 +81,7 @@ struct fm_ctx {
   FmParamsDev* d_params = nullptr;
   // staging for fm_score_batch: two chunk slots
   Arena in[2], out[2], roll, misc;
+  RowCache cache;
   cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
   std::vector<cudaEvent_t> kev;    // per-chunk kernel timing events
   int score_smem_set = 0, groups_smem_set = 0, sort_smem_set = 0, elect_smem_set = 0, count_smem_set = 0;
@@ -349,6 +385,7 @@ uint32_t fm_sizeof(uint32_t which) {
     case 7: return sizeof(fm_rollup_rec);
     case 8: return sizeof(fm_timing);
     case 9: return sizeof(fm_synth_desc);
+    case 10: return sizeof(fm_cache_stats);
     default: return 0;
   }
 }
@@ -453,7 +490,7 @@ int32_t fm_ctx_destroy(fm_ctx* c) {
     if (c->out_free[i]) cudaEventDestroy(c->out_free[i]);
   }
   for (cudaEvent_t e : c->kev) cudaEventDestroy(e);
-  c->roll.release(); c->misc.release();
+  c->roll.release(); c->misc.release(); c->cache.release();
   if (c->d_params) cudaFree(c->d_params);
   if (c->ev_a) cudaEventDestroy(c->ev_a);
   if (c->ev_b) cudaEventDestroy(c->ev_b);
@@ -561,8 +598,105 @@ int32_t fm_score_batch_device(fm_ctx* c, const fm_batch* b, void* d_out, fm_rank
   return FM_OK;
 }
 
-int32_t fm_score_batch(fm_ctx* c, const fm_batch* b, void* out, fm_rank_aux* out_aux,
-                       fm_rollup_rec* out_api, fm_rollup_rec* out_svc, fm_timing* timing) {
+}  // extern "C"
+
+namespace {
+
+// (Re)build the cache storage for this batch's row layout.  Returns false when the cache is off or
+// cannot hold a single row.
+int32_t cache_prepare(fm_ctx* c, const fm_batch* b, bool canary, bool* on) {
+  RowCache& k = c->cache;
+  *on = false;
+  if (k.max_bytes == 0) return FM_OK;
+  const uint32_t nb = canary ? b->n_base : 0u, pb = canary ? b->base_pitch : 0u;
+  const uint32_t nh = b->hist ? b->n_hist : 0u, ph = b->hist ? b->hist_pitch : 0u;
+  const uint64_t row_bytes = 4ull * ((uint64_t)pb + ph);
+  if (row_bytes == 0) return FM_OK;                       // nothing cacheable in this batch
+  if (k.cap && (k.n_base != nb || k.base_pitch != pb || k.n_hist != nh || k.hist_pitch != ph)) k.release();
+  if (!k.cap) {
+    const uint64_t cap = std::min<uint64_t>(k.max_bytes / row_bytes, 0xFFFFFFF0ull);
+    if (cap == 0) return FM_OK;
+    if (pb) FM_CK(c, cudaMalloc(&k.d_base, cap * pb * 4ull));
+    if (ph) {
+      cudaError_t e = cudaMalloc(&k.d_hist, cap * ph * 4ull);
+      if (e != cudaSuccess) { k.release(); FM_CK(c, e); }
+    }
+    k.cap = cap; k.n_base = nb; k.base_pitch = pb; k.n_hist = nh; k.hist_pitch = ph;
+    k.slot_id.assign(cap, 0); k.slot_epoch.assign(cap, 0); k.slot_blen.assign(cap, 0); k.slot_hlen.assign(cap, 0);
+    k.slot_live.assign(cap, 0);
+    k.index.reserve((size_t)std::min<uint64_t>(cap, 1u << 22));
+  }
+  *on = true;
+  return FM_OK;
+}
+
+// Slot of every row of the call (kNone: the cache is full of rows of this very call -> that row
+// is uploaded into the chunk buffer like an uncached one) and whether it has to be uploaded.
+void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t S, bool canary,
+                  std::vector<uint32_t>& slot, std::vector<uint8_t>& miss) {
+  slot.resize(S); miss.assign(S, 0);
+  if (++k.epoch == 0) {                                   // epoch wrapped: nobody is "in use"
+    std::fill(k.slot_epoch.begin(), k.slot_epoch.end(), 0u);
+    k.epoch = 1;
+  }
+  const bool have_prev = !k.prev_ids.empty();
+  for (uint64_t s = 0; s < S; ++s) {
+    const uint64_t id = ids[s];
+    uint32_t sl = RowCache::kNone;
+    if (have_prev && s < k.prev_ids.size() && k.prev_ids[s] == id) {
+      const uint32_t ps = k.prev_slot[s];
+      if (ps != RowCache::kNone && k.slot_live[ps] && k.slot_id[ps] == id) sl = ps;
+    }
+    if (sl == RowCache::kNone) {
+      auto it = k.index.find(id);
+      if (it != k.index.end()) sl = it->second;
+    }
+    if (sl != RowCache::kNone) {
+      ++k.hits;
+    } else {
+      // a free slot, else the least recently used one that this call has not touched
+      if (k.n_live < k.cap) {
+        while (k.slot_live[k.hand]) k.hand = (k.hand + 1) % k.cap;
+        sl = (uint32_t)k.hand;
+        k.hand = (k.hand + 1) % k.cap;
+      } else {
+        uint64_t best = k.cap; uint32_t best_age = 0;
+        for (uint64_t probe = 0; probe < std::min<uint64_t>(k.cap, 64); ++probe) {   // clock: 64 candidates
+          const uint64_t q = (k.hand + probe) % k.cap;
+          if (k.slot_epoch[q] == k.epoch) continue;
+          const uint32_t age = k.epoch - k.slot_epoch[q];
+          if (best == k.cap || age > best_age) { best = q; best_age = age; }
+        }
+        if (best == k.cap) {
+          for (uint64_t q = 0; q < k.cap; ++q) if (k.slot_epoch[q] != k.epoch) { best = q; break; }
+        }
+        if (best != k.cap) {
+          k.index.erase(k.slot_id[best]);
+          k.slot_live[best] = 0; --k.n_live; ++k.evictions;
+          sl = (uint32_t)best;
+          k.hand = (best + 1) % k.cap;
+        }
+      }
+      if (sl != RowCache::kNone) {
+        k.slot_live[sl] = 1; ++k.n_live;
+        k.slot_id[sl] = id;
+        k.slot_blen[sl] = canary ? (b->base_len ? std::min(b->base_len[s], b->n_base) : b->n_base) : 0u;
+        k.slot_hlen[sl] = b->hist ? (b->hist_len ? std::min(b->hist_len[s], b->n_hist) : b->n_hist) : 0u;
+        k.index[id] = sl;
+        miss[s] = 1; ++k.misses;
+      } else {
+        miss[s] = 1; ++k.uncached;
+      }
+    }
+    if (sl != RowCache::kNone) k.slot_epoch[sl] = k.epoch;
+    slot[s] = sl;
+  }
+  k.prev_ids.assign(ids, ids + S);
+  k.prev_slot = slot;
+}
+
+int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, void* out, fm_rank_aux* out_aux,
+                         fm_rollup_rec* out_api, fm_rollup_rec* out_svc, fm_timing* timing) {
   int32_t rc = validate_batch(c, b, out);
   if (rc != FM_OK) return rc;
   FM_CK(c, cudaSetDevice(c->device));
@@ -573,6 +707,31 @@ int32_t fm_score_batch(fm_ctx* c, const fm_batch* b, void* out, fm_rank_aux* out
   const bool roll = b->api_id && out_api && b->n_apis;
   const bool roll_svc = roll && out_svc && b->api_service && b->n_services;
   const size_t rsz = rec_size(b->record_kind);
+
+  // row cache: slot per row, which rows still have to come over PCIe
+  bool cached = false;
+  std::vector<uint32_t> slot;
+  std::vector<uint8_t> miss;
+  std::vector<uint32_t> eff_blen, eff_hlen;
+  if (row_ids) {
+    rc = cache_prepare(c, b, canary, &cached);
+    if (rc != FM_OK) return rc;
+  }
+  RowCache& kc = c->cache;
+  if (cached) {
+    cache_assign(kc, b, row_ids, S, canary, slot, miss);
+    // lengths: a resident row keeps the length it was stored with
+    if (canary && b->base_len) {
+      eff_blen.resize(S);
+      for (uint64_t s = 0; s < S; ++s) eff_blen[s] = slot[s] != RowCache::kNone ? kc.slot_blen[slot[s]] : std::min(b->base_len[s], b->n_base);
+    }
+    if (b->hist && b->hist_len) {
+      eff_hlen.resize(S);
+      for (uint64_t s = 0; s < S; ++s) eff_hlen[s] = slot[s] != RowCache::kNone ? kc.slot_hlen[slot[s]] : std::min(b->hist_len[s], b->n_hist);
+    }
+  }
+  const uint32_t* h_blen = cached && !eff_blen.empty() ? eff_blen.data() : b->base_len;
+  const uint32_t* h_hlen = cached && !eff_hlen.empty() ? eff_hlen.data() : b->hist_len;
 
   // chunking: ~64 MB of rows per chunk, two slots in flight
   const size_t row_bytes = 4 * ((size_t)b->cur_pitch + (canary ? b->base_pitch : 0) + (b->hist ? b->hist_pitch : 0));
@@ -592,6 +751,7 @@ int32_t fm_score_batch(fm_ctx* c, const fm_batch* b, void* out, fm_rank_aux* out
   const size_t o_hlen = o; o += (b->hist && b->hist_len) ? al(chunk * 4) : 0;
   const size_t o_mt = o;   o += b->metric_type ? al(chunk) : 0;
   const size_t o_api = o;  o += roll ? al(chunk * 4) : 0;
+  const size_t o_slot = o; o += cached ? al(chunk * 4) : 0;
   const size_t in_bytes = o;
   const size_t o_rec = 0;
   const size_t o_aux = al(chunk * rsz);
@@ -619,26 +779,65 @@ int32_t fm_score_batch(fm_ctx* c, const fm_batch* b, void* out, fm_rank_aux* out
 
   uint32_t launches = 0;
   uint64_t h2d = 0, d2h = 0;
+  // an error inside the loop must not leave copies in flight on buffers the caller owns
+  auto drain = [&]() { cudaStreamSynchronize(c->s_h2d); cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->s_d2h); };
+#define FM_CKL(call)                                                                  \
+  do {                                                                                \
+    cudaError_t e__ = (call);                                                         \
+    if (e__ != cudaSuccess) {                                                         \
+      drain();                                                                        \
+      return fail(c, e__ == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_CUDA,       \
+                  "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__,  \
+                  __LINE__);                                                          \
+    }                                                                                 \
+  } while (0)
   for (uint64_t ci = 0; ci < n_chunks; ++ci) {
     const int s = (int)(ci & 1);
     const uint64_t s0 = ci * chunk, n = std::min(chunk, S - s0);
     char* din = static_cast<char*>(c->in[s].p);
     char* dout = static_cast<char*>(c->out[s].p);
     // host -> device on the copy stream, once the slot's previous kernel is done
-    if (ci >= 2) FM_CK(c, cudaStreamWaitEvent(c->s_h2d, c->in_free[s], 0));
-    auto up = [&](size_t off, const void* src, size_t bytes) -> cudaError_t {
+    if (ci >= 2) FM_CKL(cudaStreamWaitEvent(c->s_h2d, c->in_free[s], 0));
+    auto up = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
       h2d += bytes;
-      return cudaMemcpyAsync(din + off, src, bytes, cudaMemcpyHostToDevice, c->s_h2d);
+      return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->s_h2d);
     };
-    FM_CK(c, up(o_cur, b->cur + s0 * b->cur_pitch, n * b->cur_pitch * 4));
-    if (canary) FM_CK(c, up(o_base, b->base + s0 * b->base_pitch, n * b->base_pitch * 4));
-    if (b->hist) FM_CK(c, up(o_hist, b->hist + s0 * b->hist_pitch, n * b->hist_pitch * 4));
-    if (b->cur_len) FM_CK(c, up(o_clen, b->cur_len + s0, n * 4));
-    if (canary && b->base_len) FM_CK(c, up(o_blen, b->base_len + s0, n * 4));
-    if (b->hist && b->hist_len) FM_CK(c, up(o_hlen, b->hist_len + s0, n * 4));
-    if (b->metric_type) FM_CK(c, up(o_mt, b->metric_type + s0, n));
-    if (roll) FM_CK(c, up(o_api, b->api_id + s0, n * 4));
-    FM_CK(c, cudaEventRecord(c->in_ready[s], c->s_h2d));
+    FM_CKL(up(din + o_cur, b->cur + s0 * b->cur_pitch, n * b->cur_pitch * 4));
+    if (!cached) {
+      if (canary) FM_CKL(up(din + o_base, b->base + s0 * b->base_pitch, n * b->base_pitch * 4));
+      if (b->hist) FM_CKL(up(din + o_hist, b->hist + s0 * b->hist_pitch, n * b->hist_pitch * 4));
+    } else {
+      // rows the cache does not hold yet: one copy per run of consecutive rows whose slots are
+      // consecutive too (a cold cache hands out consecutive slots, so runs are long); rows that
+      // found no slot go straight into the chunk buffer
+      uint64_t i = 0;
+      while (i < n) {
+        if (!miss[s0 + i]) { ++i; continue; }
+        const uint32_t sl0 = slot[s0 + i];
+        uint64_t j = i + 1;
+        if (sl0 == RowCache::kNone) { while (j < n && miss[s0 + j] && slot[s0 + j] == RowCache::kNone) ++j; }
+        else { while (j < n && miss[s0 + j] && slot[s0 + j] == sl0 + (uint32_t)(j - i)) ++j; }
+        const uint64_t r = j - i;
+        if (canary) {
+          float* dst = sl0 == RowCache::kNone ? reinterpret_cast<float*>(din + o_base) + i * b->base_pitch
+                                              : kc.d_base + (uint64_t)sl0 * b->base_pitch;
+          FM_CKL(up(dst, b->base + (s0 + i) * b->base_pitch, r * b->base_pitch * 4));
+        }
+        if (b->hist) {
+          float* dst = sl0 == RowCache::kNone ? reinterpret_cast<float*>(din + o_hist) + i * b->hist_pitch
+                                              : kc.d_hist + (uint64_t)sl0 * b->hist_pitch;
+          FM_CKL(up(dst, b->hist + (s0 + i) * b->hist_pitch, r * b->hist_pitch * 4));
+        }
+        i = j;
+      }
+      FM_CKL(up(din + o_slot, slot.data() + s0, n * 4));
+    }
+    if (b->cur_len) FM_CKL(up(din + o_clen, b->cur_len + s0, n * 4));
+    if (canary && b->base_len) FM_CKL(up(din + o_blen, h_blen + s0, n * 4));
+    if (b->hist && b->hist_len) FM_CKL(up(din + o_hlen, h_hlen + s0, n * 4));
+    if (b->metric_type) FM_CKL(up(din + o_mt, b->metric_type + s0, n));
+    if (roll) FM_CKL(up(din + o_api, b->api_id + s0, n * 4));
+    FM_CKL(cudaEventRecord(c->in_ready[s], c->s_h2d));
 
     // score on the compute stream
     fm_batch db = *b;
@@ -653,42 +852,47 @@ int32_t fm_score_batch(fm_ctx* c, const fm_batch* b, void* out, fm_rank_aux* out
     db.api_id = roll ? reinterpret_cast<const uint32_t*>(din + o_api) : nullptr;
     Plan pl;
     rc = plan_score(c, &db, &pl);
-    if (rc != FM_OK) return rc;
+    if (rc != FM_OK) { drain(); return rc; }
     pl.a.out = dout + o_rec;
     pl.a.aux = out_aux ? reinterpret_cast<fm_rank_aux*>(dout + o_aux) : nullptr;
     pl.a.api = roll ? d_api : nullptr;
-    FM_CK(c, cudaStreamWaitEvent(c->stream, c->in_ready[s], 0));
-    if (ci >= 2) FM_CK(c, cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
-    FM_CK(c, cudaEventRecord(c->kev[2 * ci], c->stream));
+    FM_CKL(cudaStreamWaitEvent(c->stream, c->in_ready[s], 0));
+    if (ci >= 2) FM_CKL(cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
+    FM_CKL(cudaEventRecord(c->kev[2 * ci], c->stream));
+    if (cached) {   // resident rows -> the chunk's row matrices (HBM to HBM)
+      const uint32_t* d_slot = reinterpret_cast<const uint32_t*>(din + o_slot);
+      if (canary) launches += fm_launch_gather_rows(kc.d_base, b->base_pitch, d_slot, reinterpret_cast<float*>(din + o_base), n, c->stream);
+      if (b->hist) launches += fm_launch_gather_rows(kc.d_hist, b->hist_pitch, d_slot, reinterpret_cast<float*>(din + o_hist), n, c->stream);
+    }
     launches += launch_plan(pl, c->stream);
-    FM_CK(c, cudaGetLastError());
-    FM_CK(c, cudaEventRecord(c->kev[2 * ci + 1], c->stream));
-    FM_CK(c, cudaEventRecord(c->in_free[s], c->stream));
-    FM_CK(c, cudaEventRecord(c->out_ready[s], c->stream));
+    FM_CKL(cudaGetLastError());
+    FM_CKL(cudaEventRecord(c->kev[2 * ci + 1], c->stream));
+    FM_CKL(cudaEventRecord(c->in_free[s], c->stream));
+    FM_CKL(cudaEventRecord(c->out_ready[s], c->stream));
 
     // device -> host on the read-back stream
-    FM_CK(c, cudaStreamWaitEvent(c->s_d2h, c->out_ready[s], 0));
-    FM_CK(c, cudaMemcpyAsync(static_cast<char*>(out) + s0 * rsz, dout + o_rec, n * rsz, cudaMemcpyDeviceToHost, c->s_d2h));
+    FM_CKL(cudaStreamWaitEvent(c->s_d2h, c->out_ready[s], 0));
+    FM_CKL(cudaMemcpyAsync(static_cast<char*>(out) + s0 * rsz, dout + o_rec, n * rsz, cudaMemcpyDeviceToHost, c->s_d2h));
     d2h += n * rsz;
     if (out_aux) {
-      FM_CK(c, cudaMemcpyAsync(out_aux + s0, dout + o_aux, n * sizeof(fm_rank_aux), cudaMemcpyDeviceToHost, c->s_d2h));
+      FM_CKL(cudaMemcpyAsync(out_aux + s0, dout + o_aux, n * sizeof(fm_rank_aux), cudaMemcpyDeviceToHost, c->s_d2h));
       d2h += n * sizeof(fm_rank_aux);
     }
-    FM_CK(c, cudaEventRecord(c->out_free[s], c->s_d2h));
+    FM_CKL(cudaEventRecord(c->out_free[s], c->s_d2h));
   }
   if (roll) {
     launches += fm_launch_rollup_finalize(d_api, b->n_apis, d_api_service, d_svc, b->n_services, c->stream);
-    FM_CK(c, cudaGetLastError());
-    FM_CK(c, cudaMemcpyAsync(out_api, d_api, (size_t)b->n_apis * sizeof(fm_rollup_rec), cudaMemcpyDeviceToHost, c->stream));
+    FM_CKL(cudaGetLastError());
+    FM_CKL(cudaMemcpyAsync(out_api, d_api, (size_t)b->n_apis * sizeof(fm_rollup_rec), cudaMemcpyDeviceToHost, c->stream));
     d2h += (size_t)b->n_apis * sizeof(fm_rollup_rec);
     if (roll_svc) {
-      FM_CK(c, cudaMemcpyAsync(out_svc, d_svc, (size_t)b->n_services * sizeof(fm_rollup_rec), cudaMemcpyDeviceToHost, c->stream));
+      FM_CKL(cudaMemcpyAsync(out_svc, d_svc, (size_t)b->n_services * sizeof(fm_rollup_rec), cudaMemcpyDeviceToHost, c->stream));
       d2h += (size_t)b->n_services * sizeof(fm_rollup_rec);
     }
   }
-  FM_CK(c, cudaStreamSynchronize(c->s_h2d));
-  FM_CK(c, cudaStreamSynchronize(c->stream));
-  FM_CK(c, cudaStreamSynchronize(c->s_d2h));
+#undef FM_CKL
+  cudaError_t e1 = cudaStreamSynchronize(c->s_h2d), e2 = cudaStreamSynchronize(c->stream), e3 = cudaStreamSynchronize(c->s_d2h);
+  FM_CK(c, e1); FM_CK(c, e2); FM_CK(c, e3);
   if (timing) {
     float tot = 0.f;
     for (uint64_t ci = 0; ci < n_chunks; ++ci) {
@@ -699,6 +903,49 @@ int32_t fm_score_batch(fm_ctx* c, const fm_batch* b, void* out, fm_rank_aux* out
     timing->kernel_ms = tot; timing->main_kernel_ms = tot; timing->launches = launches;
     timing->h2d_bytes = h2d; timing->d2h_bytes = d2h;
   }
+  return FM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t fm_score_batch(fm_ctx* c, const fm_batch* b, void* out, fm_rank_aux* out_aux,
+                       fm_rollup_rec* out_api, fm_rollup_rec* out_svc, fm_timing* timing) {
+  return score_batch_impl(c, b, nullptr, out, out_aux, out_api, out_svc, timing);
+}
+
+int32_t fm_score_batch_cached(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, void* out, fm_rank_aux* out_aux,
+                              fm_rollup_rec* out_api, fm_rollup_rec* out_svc, fm_timing* timing) {
+  if (!c) return FM_E_INVALID;
+  if (!row_ids && b && b->n_series) return fail(c, FM_E_INVALID, "fm_score_batch_cached: row_ids is NULL");
+  return score_batch_impl(c, b, row_ids, out, out_aux, out_api, out_svc, timing);
+}
+
+int32_t fm_cache_configure(fm_ctx* c, uint64_t max_bytes) {
+  if (!c) return FM_E_INVALID;
+  FM_CK(c, cudaSetDevice(c->device));
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  c->cache.release();
+  c->cache.max_bytes = max_bytes;
+  c->cache.hits = c->cache.misses = c->cache.evictions = c->cache.uncached = 0;
+  return FM_OK;
+}
+
+int32_t fm_cache_get_stats(fm_ctx* c, fm_cache_stats* out) {
+  if (!c || !out) return FM_E_INVALID;
+  const RowCache& k = c->cache;
+  out->max_bytes = k.max_bytes; out->capacity_rows = k.cap; out->resident_rows = k.n_live;
+  out->hits = k.hits; out->misses = k.misses; out->evictions = k.evictions; out->uncached = k.uncached;
+  out->row_bytes = 4ull * ((uint64_t)k.base_pitch + k.hist_pitch);
+  return FM_OK;
+}
+
+int32_t fm_cache_query(fm_ctx* c, const uint64_t* row_ids, uint64_t n, uint8_t* resident_out) {
+  if (!c) return FM_E_INVALID;
+  if (n && (!row_ids || !resident_out)) return fail(c, FM_E_INVALID, "fm_cache_query: null pointer");
+  const RowCache& k = c->cache;
+  for (uint64_t i = 0; i < n; ++i) resident_out[i] = k.cap && k.index.find(row_ids[i]) != k.index.end() ? 1 : 0;
   return FM_OK;
 }
 

@@ -74,6 +74,9 @@ cudaError_t fm_canary_elect_smem_attr(int bytes);
 int fm_launch_rollup_finalize(fm_rollup_rec* api, uint32_t n_apis, const uint32_t* api_service,
                               fm_rollup_rec* svc, uint32_t n_services, cudaStream_t st);
 int fm_launch_rollup_finalize_one(fm_rollup_rec* recs, uint64_t n, cudaStream_t st);
+// fm_kernels.cu: cache rows (slot per row, 0xFFFFFFFF = skip) -> contiguous row matrix
+int fm_launch_gather_rows(const float* cache, uint32_t pitch, const uint32_t* d_slot, float* dst, uint64_t n,
+                          cudaStream_t st);
 int fm_launch_rank_dump(const float* d_cur, uint32_t n_cur, const float* d_base, uint32_t n_base,
                         float* d_sorted /* pow2 scratch */, uint32_t cap, uint32_t* d_r2,
                         cudaStream_t st);

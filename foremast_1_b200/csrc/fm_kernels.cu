@@ -438,6 +438,17 @@ __global__ void k_synth_rows(fm_synth_desc d, float* out, uint32_t n, uint32_t p
   for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < pitch; t += gridDim.x * blockDim.x)
     out[row * pitch + t] = t < n ? fm_synth_sample(d.seed, &sp, id, kind, t) : 0.0f;
 }
+// rows resident in the cache -> the chunk's row matrix: one CTA per row, 128-bit copies; rows
+// without a slot were uploaded into place by the host
+__global__ void __launch_bounds__(128) k_gather_rows(const float4* __restrict__ cache, uint32_t pitch4,
+                                                     const uint32_t* __restrict__ slot, float4* __restrict__ dst) {
+  const uint32_t sl = slot[blockIdx.x];
+  if (sl == 0xFFFFFFFFu) return;
+  const float4* src = cache + (uint64_t)sl * pitch4;
+  float4* d = dst + (uint64_t)blockIdx.x * pitch4;
+  for (uint32_t i = threadIdx.x; i < pitch4; i += 128) d[i] = fm_ldg_stream(src + i);
+}
+
 __global__ void k_synth_types(fm_synth_desc d, uint8_t* mt) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < d.n_series) mt[i] = (uint8_t)fm_synth_type(d.config, d.row_ids ? d.row_ids[i] : d.first_series + i);
@@ -475,6 +486,14 @@ int fm_launch_rollup_finalize(fm_rollup_rec* api, uint32_t n_apis, const uint32_
     ++n;
   }
   return n;
+}
+
+int fm_launch_gather_rows(const float* cache, uint32_t pitch, const uint32_t* d_slot, float* dst, uint64_t n,
+                          cudaStream_t st) {
+  if (!n || !pitch) return 0;
+  k_gather_rows<<<(unsigned)n, 128, 0, st>>>(reinterpret_cast<const float4*>(cache), pitch >> 2, d_slot,
+                                             reinterpret_cast<float4*>(dst));
+  return 1;
 }
 
 int fm_launch_rollup_finalize_one(fm_rollup_rec* recs, uint64_t n, cudaStream_t st) {

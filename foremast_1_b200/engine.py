@@ -103,7 +103,9 @@ class Context:
     # ---- host-row scoring -------------------------------------------------
     def score(self, cur, base=None, hist=None, *, strategy=A.FM_STRAT_CANARY, cur_len=None,
               base_len=None, hist_len=None, metric_type=None, api_id=None, api_service=None,
-              n_apis=0, n_services=0, record_kind=A.FM_REC_FULL, want_aux=False):
+              n_apis=0, n_services=0, record_kind=A.FM_REC_FULL, want_aux=False, row_ids=None):
+        """row_ids (uint64 per series): score through the device-resident row cache
+        (fm_score_batch_cached; see cache_configure)."""
         cur, n_cur = _as_matrix(cur)
         base, n_base = _as_matrix(base)
         hist, n_hist = _as_matrix(hist)
@@ -140,9 +142,31 @@ class Context:
         api = np.zeros(int(n_apis), A.ROLLUP_REC) if ai is not None else None
         svc = np.zeros(int(n_services), A.ROLLUP_REC) if (ai is not None and asv is not None) else None
         t = A.Timing()
-        self._ck(self._lib.fm_score_batch(self._h, C.byref(b), A.ptr(rec), A.ptr(aux), A.ptr(api),
-                                          A.ptr(svc), C.byref(t)))
+        if row_ids is None:
+            self._ck(self._lib.fm_score_batch(self._h, C.byref(b), A.ptr(rec), A.ptr(aux), A.ptr(api),
+                                              A.ptr(svc), C.byref(t)))
+        else:
+            ids = np.ascontiguousarray(row_ids, dtype=np.uint64)
+            assert ids.size == S
+            keep.append(ids)
+            self._ck(self._lib.fm_score_batch_cached(self._h, C.byref(b), A.ptr(ids), A.ptr(rec), A.ptr(aux),
+                                                     A.ptr(api), A.ptr(svc), C.byref(t)))
         return {"rec": rec, "aux": aux, "api": api, "svc": svc, "timing": t, "batch": b, "_keep": keep}
+
+    # ---- device-resident row cache (MAX_CACHE_SIZE) ---------------------------
+    def cache_configure(self, max_bytes):
+        self._ck(self._lib.fm_cache_configure(self._h, int(max_bytes)))
+
+    def cache_stats(self):
+        st = A.CacheStats()
+        self._ck(self._lib.fm_cache_get_stats(self._h, C.byref(st)))
+        return {n: int(getattr(st, n)) for n, _ in A.CacheStats._fields_}
+
+    def cache_query(self, row_ids):
+        ids = np.ascontiguousarray(row_ids, dtype=np.uint64)
+        res = np.zeros(ids.size, np.uint8)
+        self._ck(self._lib.fm_cache_query(self._h, A.ptr(ids), ids.size, A.ptr(res)))
+        return res.astype(bool)
 
     def score_groups(self, cur, group_offsets, hist, *, cur_len=None, hist_len=None, metric_type=None):
         cur, n_cur = _as_matrix(cur)
@@ -210,11 +234,16 @@ class Context:
                                                  C.c_void_p(d_api), C.c_void_p(d_svc),
                                                  C.byref(timing) if timing is not None else None))
 
-    def score_host(self, batch, out, aux=None, api=None, svc=None, timing=None):
-        """fm_score_batch on raw host pointers (pinned buffers from alloc_pinned)."""
-        self._ck(self._lib.fm_score_batch(self._h, C.byref(batch), C.c_void_p(out), C.c_void_p(aux),
-                                          C.c_void_p(api), C.c_void_p(svc),
-                                          C.byref(timing) if timing is not None else None))
+    def score_host(self, batch, out, aux=None, api=None, svc=None, timing=None, row_ids=None):
+        """fm_score_batch (fm_score_batch_cached with row_ids, a host pointer to uint64 ids) on raw
+        host pointers (pinned buffers from alloc_pinned)."""
+        tp = C.byref(timing) if timing is not None else None
+        if row_ids is None:
+            self._ck(self._lib.fm_score_batch(self._h, C.byref(batch), C.c_void_p(out), C.c_void_p(aux),
+                                              C.c_void_p(api), C.c_void_p(svc), tp))
+        else:
+            self._ck(self._lib.fm_score_batch_cached(self._h, C.byref(batch), C.c_void_p(row_ids), C.c_void_p(out),
+                                                     C.c_void_p(aux), C.c_void_p(api), C.c_void_p(svc), tp))
 
     def score_groups_device(self, gbatch, d_out, d_svc=None, timing=None):
         self._ck(self._lib.fm_score_groups_device(self._h, C.byref(gbatch), C.c_void_p(d_out), C.c_void_p(d_svc),

@@ -283,6 +283,38 @@ int32_t fm_score_batch(fm_ctx* ctx, const fm_batch* batch, void* out_records,
                        fm_rank_aux* out_aux, fm_rollup_rec* out_api,
                        fm_rollup_rec* out_svc, fm_timing* timing);
 
+/* Device-resident row cache: MAX_CACHE_SIZE, "max cached model size"
+ * (foremast-brain/README.md:30).  A job is re-judged on every poll until its
+ * endTime (docs/guides/design.md:43); its baseline and 7-day history do not
+ * change between polls, only the current window does.
+ *
+ * fm_cache_configure  max_bytes of HBM for resident rows on this ctx (0 = off,
+ *                     the default; any call drops what is resident).
+ * fm_score_batch_cached  fm_score_batch with one 64-bit id per series (the
+ *                     caller's choice, e.g. hash of job id and metric alias).
+ *                     Baseline / history rows whose id is resident are NOT read
+ *                     from the host (those host rows need not even be valid:
+ *                     ask fm_cache_query first and skip the fetch); the others
+ *                     are uploaded and become resident, least recently scored
+ *                     rows making room.  Current rows, metric types and API ids
+ *                     are uploaded every call.  A resident row keeps the length
+ *                     it was stored with (pass base_len / hist_len on every call
+ *                     if any row is ragged).  Results are identical to
+ *                     fm_score_batch on the same rows.  One row layout (n_base,
+ *                     base_pitch, n_hist, hist_pitch) is resident at a time.
+ * fm_cache_query      resident_out[i] = 1 if row_ids[i] is resident.
+ * fm_cache_get_stats  counters since fm_cache_configure. */
+typedef struct {
+  uint64_t max_bytes, row_bytes, capacity_rows, resident_rows;
+  uint64_t hits, misses, evictions, uncached;   /* uncached: rows of a call larger than the cache */
+} fm_cache_stats;
+int32_t fm_cache_configure(fm_ctx* ctx, uint64_t max_bytes);
+int32_t fm_score_batch_cached(fm_ctx* ctx, const fm_batch* batch, const uint64_t* row_ids,
+                              void* out_records, fm_rank_aux* out_aux, fm_rollup_rec* out_api,
+                              fm_rollup_rec* out_svc, fm_timing* timing);
+int32_t fm_cache_query(fm_ctx* ctx, const uint64_t* row_ids, uint64_t n, uint8_t* resident_out);
+int32_t fm_cache_get_stats(fm_ctx* ctx, fm_cache_stats* out);
+
 /* Same, with every pointer in `batch` and every output a DEVICE pointer.
  * Asynchronous on the ctx stream unless `timing` is non-NULL (then it
  * synchronises to read the events). */
