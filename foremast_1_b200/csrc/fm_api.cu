@@ -639,6 +639,7 @@ void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t 
     std::fill(k.slot_epoch.begin(), k.slot_epoch.end(), 0u);
     k.epoch = 1;
   }
+  // pass 1: rows that are resident (and protect their slots from this call's evictions)
   const bool have_prev = !k.prev_ids.empty();
   for (uint64_t s = 0; s < S; ++s) {
     const uint64_t id = ids[s];
@@ -651,44 +652,51 @@ void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t 
       auto it = k.index.find(id);
       if (it != k.index.end()) sl = it->second;
     }
-    if (sl != RowCache::kNone) {
-      ++k.hits;
+    if (sl != RowCache::kNone) { ++k.hits; k.slot_epoch[sl] = k.epoch; }
+    slot[s] = sl;
+  }
+  // pass 2: a slot for every other row: a free one, else the least recently scored one that this
+  // call does not use (clock hand, 64 candidates); none left -> the row stays uncached
+  for (uint64_t s = 0; s < S; ++s) {
+    if (slot[s] != RowCache::kNone) continue;
+    const uint64_t id = ids[s];
+    auto it = k.index.find(id);                            // the same id twice in one call
+    if (it != k.index.end()) { slot[s] = it->second; ++k.hits; continue; }
+    uint32_t sl = RowCache::kNone;
+    if (k.n_live < k.cap) {
+      while (k.slot_live[k.hand]) k.hand = (k.hand + 1) % k.cap;
+      sl = (uint32_t)k.hand;
+      k.hand = (k.hand + 1) % k.cap;
     } else {
-      // a free slot, else the least recently used one that this call has not touched
-      if (k.n_live < k.cap) {
-        while (k.slot_live[k.hand]) k.hand = (k.hand + 1) % k.cap;
-        sl = (uint32_t)k.hand;
-        k.hand = (k.hand + 1) % k.cap;
-      } else {
-        uint64_t best = k.cap; uint32_t best_age = 0;
-        for (uint64_t probe = 0; probe < std::min<uint64_t>(k.cap, 64); ++probe) {   // clock: 64 candidates
-          const uint64_t q = (k.hand + probe) % k.cap;
-          if (k.slot_epoch[q] == k.epoch) continue;
-          const uint32_t age = k.epoch - k.slot_epoch[q];
-          if (best == k.cap || age > best_age) { best = q; best_age = age; }
-        }
-        if (best == k.cap) {
-          for (uint64_t q = 0; q < k.cap; ++q) if (k.slot_epoch[q] != k.epoch) { best = q; break; }
-        }
-        if (best != k.cap) {
-          k.index.erase(k.slot_id[best]);
-          k.slot_live[best] = 0; --k.n_live; ++k.evictions;
-          sl = (uint32_t)best;
-          k.hand = (best + 1) % k.cap;
-        }
+      uint64_t best = k.cap; uint32_t best_age = 0;
+      for (uint64_t probe = 0; probe < std::min<uint64_t>(k.cap, 64); ++probe) {
+        const uint64_t q = (k.hand + probe) % k.cap;
+        if (k.slot_epoch[q] == k.epoch) continue;
+        const uint32_t age = k.epoch - k.slot_epoch[q];
+        if (best == k.cap || age > best_age) { best = q; best_age = age; }
       }
-      if (sl != RowCache::kNone) {
-        k.slot_live[sl] = 1; ++k.n_live;
-        k.slot_id[sl] = id;
-        k.slot_blen[sl] = canary ? (b->base_len ? std::min(b->base_len[s], b->n_base) : b->n_base) : 0u;
-        k.slot_hlen[sl] = b->hist ? (b->hist_len ? std::min(b->hist_len[s], b->n_hist) : b->n_hist) : 0u;
-        k.index[id] = sl;
-        miss[s] = 1; ++k.misses;
-      } else {
-        miss[s] = 1; ++k.uncached;
+      if (best == k.cap) {
+        for (uint64_t q = 0; q < k.cap; ++q) if (k.slot_epoch[q] != k.epoch) { best = q; break; }
+      }
+      if (best != k.cap) {
+        k.index.erase(k.slot_id[best]);
+        k.slot_live[best] = 0; --k.n_live; ++k.evictions;
+        sl = (uint32_t)best;
+        k.hand = (best + 1) % k.cap;
       }
     }
-    if (sl != RowCache::kNone) k.slot_epoch[sl] = k.epoch;
+    miss[s] = 1;
+    if (sl != RowCache::kNone) {
+      k.slot_live[sl] = 1; ++k.n_live;
+      k.slot_id[sl] = id;
+      k.slot_epoch[sl] = k.epoch;
+      k.slot_blen[sl] = canary ? (b->base_len ? std::min(b->base_len[s], b->n_base) : b->n_base) : 0u;
+      k.slot_hlen[sl] = b->hist ? (b->hist_len ? std::min(b->hist_len[s], b->n_hist) : b->n_hist) : 0u;
+      k.index[id] = sl;
+      ++k.misses;
+    } else {
+      ++k.uncached;
+    }
     slot[s] = sl;
   }
   k.prev_ids.assign(ids, ids + S);
