@@ -31,6 +31,14 @@ SYMBOLS = {
     "fm_cache_configure": (C.c_int32, [C.c_void_p, C.c_uint64]),
     "fm_cache_query": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
     "fm_cache_get_stats": (C.c_int32, [C.c_void_p, C.c_void_p]),
+    "fm_pool_create": (C.c_int32, [C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_void_p)]),
+    "fm_pool_destroy": (C.c_int32, [C.c_void_p]),
+    "fm_pool_size": (C.c_int32, [C.c_void_p]),
+    "fm_pool_ctx": (C.c_void_p, [C.c_void_p, C.c_int32]),
+    "fm_pool_set_params": (C.c_int32, [C.c_void_p, C.POINTER(A.GlobalParams), C.POINTER(A.TypeParams), C.c_uint32]),
+    "fm_pool_cache_configure": (C.c_int32, [C.c_void_p, C.c_uint64]),
+    "fm_pool_score_batch": (C.c_int32, [C.c_void_p, C.POINTER(A.Batch), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fm_pool_last_error": (C.c_char_p, [C.c_void_p]),
     "fm_score_batch_device": (C.c_int32, [C.c_void_p, C.POINTER(A.Batch), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(A.Timing)]),
     "fm_score_groups": (C.c_int32, [C.c_void_p, C.POINTER(A.GroupBatch), C.c_void_p, C.c_void_p, C.POINTER(A.Timing)]),
     "fm_score_groups_device": (C.c_int32, [C.c_void_p, C.POINTER(A.GroupBatch), C.c_void_p, C.c_void_p, C.POINTER(A.Timing)]),

@@ -250,6 +250,54 @@ class Context:
                                                   C.byref(timing) if timing is not None else None))
 
 
+class Pool:
+    """Several GPUs driven from this one process (fm_pool): one ctx and one host thread per device,
+    a batch cut into contiguous ranges of series, records written into disjoint slices of one
+    output array.  devices=None: every visible GPU."""
+
+    def __init__(self, devices=None):
+        self._lib = _ffi.lib()
+        h = C.c_void_p()
+        if devices is None:
+            rc = self._lib.fm_pool_create(None, 0, C.byref(h))
+        else:
+            arr = (C.c_int32 * len(devices))(*devices)
+            rc = self._lib.fm_pool_create(arr, len(devices), C.byref(h))
+        _ffi.check(rc, None)
+        self._h = h
+        self.size = self._lib.fm_pool_size(h)
+        self.g, self.table = A.default_params()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.fm_pool_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        if rc != A.FM_OK:
+            raise _ffi.ForemastCudaError(rc, (self._lib.fm_pool_last_error(self._h) or b"").decode("utf-8", "replace"))
+
+    def set_params(self, g, table):
+        self._ck(self._lib.fm_pool_set_params(self._h, C.byref(g), table, len(table)))
+        self.g, self.table = g, table
+
+    def cache_configure(self, max_bytes_per_device):
+        self._ck(self._lib.fm_pool_cache_configure(self._h, int(max_bytes_per_device)))
+
+    def score_host(self, batch, out, aux=None, api=None, svc=None, row_ids=None):
+        """fm_pool_score_batch on raw host pointers; returns the per-device fm_timing array."""
+        t = (A.Timing * self.size)()
+        self._ck(self._lib.fm_pool_score_batch(self._h, C.byref(batch), C.c_void_p(row_ids), C.c_void_p(out),
+                                               C.c_void_p(aux), C.c_void_p(api), C.c_void_p(svc), t))
+        return t
+
+
 def synth_desc(config, n_series, n_cur, n_base, n_hist, first_series=0, seed=None, row_ids=None):
     d = A.SynthDesc()
     d.struct_size = C.sizeof(A.SynthDesc)

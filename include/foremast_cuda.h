@@ -315,6 +315,30 @@ int32_t fm_score_batch_cached(fm_ctx* ctx, const fm_batch* batch, const uint64_t
 int32_t fm_cache_query(fm_ctx* ctx, const uint64_t* row_ids, uint64_t n, uint8_t* resident_out);
 int32_t fm_cache_get_stats(fm_ctx* ctx, fm_cache_stats* out);
 
+/* Several GPUs from ONE process (one host thread and one ctx per
+ * GPU, results gathered into one pinned array; the shared-nothing brain nodes of
+ * docs/guides/design.md:37-41 collapsed into the GPUs of one box).  A pool owns a
+ * ctx per device (devices == NULL / n_devices == 0: every visible GPU; the same
+ * device may be listed twice).  fm_pool_score_batch cuts the batch into one
+ * contiguous range of series per ctx — at service boundaries when api_id /
+ * api_service are given, so every API and service is rolled up on one GPU —
+ * scores the ranges concurrently (fm_score_batch, or fm_score_batch_cached when
+ * row_ids != NULL) and writes every range's records straight into its slice of
+ * the caller's arrays.  Results are byte-identical to one ctx scoring the whole
+ * batch.  No collective and no peer access.  timing_per_device: NULL or
+ * fm_pool_size() entries.  A pool must be used from one thread at a time. */
+typedef struct fm_pool fm_pool;
+int32_t fm_pool_create(const int32_t* devices, int32_t n_devices, fm_pool** out);
+int32_t fm_pool_destroy(fm_pool* pool);
+int32_t fm_pool_size(fm_pool* pool);
+fm_ctx* fm_pool_ctx(fm_pool* pool, int32_t i);
+int32_t fm_pool_set_params(fm_pool* pool, const fm_global_params* g, const fm_type_params* table, uint32_t n_types);
+int32_t fm_pool_cache_configure(fm_pool* pool, uint64_t max_bytes_per_device);
+int32_t fm_pool_score_batch(fm_pool* pool, const fm_batch* batch, const uint64_t* row_ids, void* out_records,
+                            fm_rank_aux* out_aux, fm_rollup_rec* out_api, fm_rollup_rec* out_svc,
+                            fm_timing* timing_per_device);
+const char* fm_pool_last_error(fm_pool* pool);
+
 /* Same, with every pointer in `batch` and every output a DEVICE pointer.
  * Asynchronous on the ctx stream unless `timing` is non-NULL (then it
  * synchronises to read the events). */
