@@ -450,7 +450,7 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
   if (const char* e = getenv("FOREMAST_CUDA_STAGES")) c->force_stages = (e[0] == '1') ? 1 : (e[0] == '2' ? 2 : 0);
   if (const char* e = getenv("FOREMAST_CUDA_SLOTS")) { const int v = atoi(e); c->count_slots = (v >= 64 && v <= 8192) ? v : 0; }
   if (const char* e = getenv("FOREMAST_CUDA_WARPS")) { const int v = atoi(e); c->count_warps = (v >= 1 && v <= 32) ? v : 0; }
-  if (const char* e = getenv("FOREMAST_CUDA_MA_GROUP")) { const int v = atoi(e); c->ma_group = (v == 4 || v == 8 || v == 16 || v == 32) ? v : 0; }
+  if (const char* e = getenv("FOREMAST_CUDA_MA_GROUP")) { const int v = atoi(e); c->ma_group = (v == 2 || v == 4 || v == 8 || v == 16 || v == 32) ? v : 0; }
   c->small_table = getenv("FOREMAST_CUDA_SMALL_TABLE") != nullptr;
   FM_CKC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   FM_CKC(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
@@ -743,7 +743,8 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
 
   // chunking: ~64 MB of rows per chunk, two slots in flight
   const size_t row_bytes = 4 * ((size_t)b->cur_pitch + (canary ? b->base_pitch : 0) + (b->hist ? b->hist_pitch : 0));
-  uint64_t chunk = row_bytes ? (size_t(64) << 20) / row_bytes : S;
+  // (with resident rows the copies are small and the per-chunk launches dominate: larger chunks)
+  uint64_t chunk = row_bytes ? (size_t(cached ? 256 : 64) << 20) / row_bytes : S;
   chunk = std::max<uint64_t>(chunk, 2048);
   chunk = std::min<uint64_t>(chunk, S);
   const uint64_t n_chunks = (S + chunk - 1) / chunk;

@@ -2,7 +2,7 @@
 // window-length sweep of BASELINE.json configs[4]): historical model -> mean, sigma -> bounds ->
 // anomalous current points -> verdict -> roll-up.  Pure streaming, HBM-bound.
 //
-// A group of G lanes owns one series (G = 4, 8 or 16 by history length), so a warp works on
+// A group of G lanes owns one series (G = 2, 4, 8 or 16 by history length), so a warp works on
 // 32/G series at a time: a 60-point history is two 128-bit loads per lane, and the per-series
 // bookkeeping (reduction, fp64 square root, record) is shared by 32/G series per instruction.
 // Rows are read once with coalesced ld.global.nc.L1::no_allocate.v4 (consecutive series are
@@ -40,7 +40,7 @@ __device__ __forceinline__ void mom4(FmMom& m, const float4& q, double pivot) {
 }
 
 template <int G>
-__global__ void __launch_bounds__(256, 4) k_ma_only(const FmKArgs a) {
+__global__ void __launch_bounds__(256, (G <= 4 ? 3 : 4)) k_ma_only(const FmKArgs a) {
   constexpr int SPW = 32 / G;                    // series per warp
   const int lane = threadIdx.x & 31;
   const int gl = lane & (G - 1), grp = lane / G;
@@ -95,19 +95,27 @@ __global__ void __launch_bounds__(256, 4) k_ma_only(const FmKArgs a) {
         q[j] = r[j];
       }
     }
-    {
-      const uint32_t t = (n4 << 2) + gl;         // up to three points after the last full vector
-      if (gl < 3 && t < nh) fm_mom_add(m, __ldg(hx + t), pivot);
-    }
+    for (uint32_t t = (n4 << 2) + gl; t < nh; t += G)   // up to three points after the last full vector
+      fm_mom_add(m, __ldg(hx + t), pivot);
     const double s1 = group_sum<G>(m.s1), s2 = group_sum<G>(m.s2);
     const bool model_ok = nh >= need;
+    // mean = pivot + s1 / n and sigma = sqrt((s2 n - s1^2) / (n (n - ddof))): ONE division per
+    // series, the even lanes of a group taking the first quotient and the odd lanes the second
     double mean = 0.0, sigma = 0.0;
-    if (model_ok) {
-      const double dn = (double)nh;
-      mean = pivot + s1 / dn;
-      double m2 = s2 - s1 * s1 / dn;
-      if (m2 < 0.0) m2 = 0.0;
-      sigma = (nh > g.ddof) ? sqrt(m2 / (double)(nh - g.ddof)) : 0.0;
+    {
+      const double dn = nh ? (double)nh : 1.0;
+      const bool odd = (gl & 1) != 0;
+      const double m2n = s2 * dn - s1 * s1;
+      const double num = odd ? (m2n > 0.0 ? m2n : 0.0) : s1;
+      const double den = odd ? dn * (double)(nh > g.ddof ? nh - g.ddof : 1u) : dn;
+      const double q = num / den;
+      const double r = sqrt(odd ? q : 0.0);
+      const int base_lane = lane & ~(G - 1);
+      const double q0 = __shfl_sync(FM_FULL, q, base_lane), r1 = __shfl_sync(FM_FULL, r, base_lane + 1);
+      if (model_ok) {
+        mean = pivot + q0;
+        sigma = nh > g.ddof ? r1 : 0.0;
+      }
     }
 
     // ---- a3, a7: bounds and anomalous current points ------------------------------------------
@@ -170,7 +178,8 @@ __global__ void __launch_bounds__(256, 4) k_ma_only(const FmKArgs a) {
 }  // namespace
 
 int fm_launch_ma_only(const FmKArgs& a, int group, int grid, cudaStream_t st) {
-  if (group == 4) k_ma_only<4><<<grid, 256, 0, st>>>(a);
+  if (group == 2) k_ma_only<2><<<grid, 256, 0, st>>>(a);
+  else if (group == 4) k_ma_only<4><<<grid, 256, 0, st>>>(a);
   else if (group == 8) k_ma_only<8><<<grid, 256, 0, st>>>(a);
   else if (group == 16) k_ma_only<16><<<grid, 256, 0, st>>>(a);
   else k_ma_only<32><<<grid, 256, 0, st>>>(a);
