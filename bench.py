@@ -255,7 +255,7 @@ def secondary(ctx, sampler, peak, steps=5, warmup=3):
         bps = 4 * (n_cur + n_base + n_hist) + rdt.itemsize
         res = {"series": S, "n_cur": n_cur, "n_base": n_base, "n_hist": n_hist, "pairwise": mode,
                "kernel": canary_kernel_name(n_cur, n_base) if canary else
-               "k_ma_only<%d>" % (16 if n_hist >= 1200 else 8 if n_hist >= 200 else 4),
+               "k_ma_only<%d>" % (16 if n_hist >= 1200 else 8 if n_hist >= 400 else 4),
                "ms": ms, "series_per_s": S / (ms / 1e3), "bytes_per_series": bps,
                "achieved_GBps": S * bps / (ms / 1e3) / 1e9, "frac": S * bps / (ms / 1e3) / 1e9 / peak,
                "launches_per_step": int(t.launches), "clocks": clk}
@@ -566,7 +566,7 @@ def main():
         bps = algorithmic_bytes(w, rec_bytes)
         achieved = S * bps / (main_ms_max / args.steps / 1e3) / 1e9
         kernel = (canary_kernel_name(w["n_cur"], w["n_base"]) if w["canary"] else
-                  ("k_ma_only<%d>" % (16 if w["n_hist"] >= 1200 else 8 if w["n_hist"] >= 200 else 4)))
+                  ("k_ma_only<%d>" % (16 if w["n_hist"] >= 1200 else 8 if w["n_hist"] >= 400 else 4)))
         traffic = measured_traffic(kernel, args.workload, S) if (args.n_hist < 0 and not args.mode) else None
         line = {
             "metric": "series scored/sec", "value": value, "unit": "series/s", "n_gpus": world,

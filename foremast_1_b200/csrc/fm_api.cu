@@ -267,12 +267,14 @@ int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
 int32_t plan_ma_only(fm_ctx* c, const fm_batch* b, Plan* pl) {
   FmKArgs& a = pl->a;
   fill_common(c, b, false, a);
-  pl->regs = b->n_hist >= 1200 ? 16 : (b->n_hist >= 200 ? 8 : 4);      // lanes per series (profiles/r01/sweep_c5.md)
+  pl->regs = b->n_hist >= 1200 ? 16 : (b->n_hist >= 400 ? 8 : 4);      // lanes per series (profiles/r02/sweep_groupsize.txt)
   if (c->ma_group) pl->regs = c->ma_group;   // experiment
   const uint64_t per_warp = 32 / pl->regs;
   const uint64_t need = (b->n_series + per_warp * 8 - 1) / (per_warp * 8);   // 8 warps per CTA
   pl->wpc = 8;
-  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * 8, need));
+  // persistent grid = the CTAs that are resident at once (64 registers x 256 threads: 4 per SM; the
+  // 2-lane form 3 per SM), so that there is no second, partial wave
+  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * (pl->regs <= 2 ? 3 : 4), need));
   pl->fast = true; pl->kind = 4;
   return FM_OK;
 }

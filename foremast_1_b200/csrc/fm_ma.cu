@@ -13,6 +13,7 @@
 // 78 % at 240, 95 % at 480, >100 % from 960 on (profiles/r01/sweep_c5.md).
 #include <cstdint>
 #include <cuda_runtime.h>
+#include <math_constants.h>
 
 #include "fm_device.cuh"
 
@@ -40,7 +41,7 @@ __device__ __forceinline__ void mom4(FmMom& m, const float4& q, double pivot) {
 }
 
 template <int G>
-__global__ void __launch_bounds__(256, (G <= 4 ? 3 : 4)) k_ma_only(const FmKArgs a) {
+__global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs a) {
   constexpr int SPW = 32 / G;                    // series per warp
   const int lane = threadIdx.x & 31;
   const int gl = lane & (G - 1), grp = lane / G;
@@ -72,7 +73,6 @@ __global__ void __launch_bounds__(256, (G <= 4 ? 3 : 4)) k_ma_only(const FmKArgs
     // ---- a2: pivoted moments of the history row ---------------------------------------------
     // software pipelined: the next four 16-byte loads of a lane are in flight while the current
     // four are accumulated (8 loads = 128 B per lane outstanding)
-    const double pivot = nh ? (double)__ldg(hx) : 0.0;
     FmMom m = {0.0, 0.0};
     const uint32_t n4 = nh >> 2;
     float4 q[4];
@@ -81,6 +81,10 @@ __global__ void __launch_bounds__(256, (G <= 4 ? 3 : 4)) k_ma_only(const FmKArgs
       q[j] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (gl + j * G < n4) q[j] = fm_ldg_stream(h4 + gl + j * G);
     }
+    // pivot = the row's first sample: it is in the first vector of the group's first lane (rows
+    // shorter than one vector fetch it on their own)
+    const float p0 = __shfl_sync(FM_FULL, q[0].x, lane & ~(G - 1));
+    const double pivot = nh >= 4u ? (double)p0 : (nh ? (double)__ldg(hx) : 0.0);
     for (uint32_t i = gl; i < n4max; i += 4 * G) {
       float4 r[4];
 #pragma unroll
@@ -126,22 +130,23 @@ __global__ void __launch_bounds__(256, (G <= 4 ? 3 : 4)) k_ma_only(const FmKArgs
     if (lo < tp.min_lower_bound) lo = tp.min_lower_bound;
     uint32_t mlo = 0, mhi = 0;                   // anomaly mask of the (<= 64) current points
     if (model_ok) {
-      const bool chk_up = (tp.bound_mask & 1u) != 0, chk_lo = (tp.bound_mask & 2u) != 0;
       // fp32 x against an fp64 bound, exactly, without converting every x: x > up <=> x > rd(up)
       // (rd(up) is the largest float <= up, so the next float above it exceeds up), and
-      // x < lo <=> x < ru(lo); NaN bounds compare false either way.
-      const float up_f = __double2float_rd(up), lo_f = __double2float_ru(lo);
+      // x < lo <=> x < ru(lo); NaN bounds compare false either way.  A side that is not checked
+      // gets an infinite bound; the points behind the row's end are masked once at the end: no
+      // branch and no index test per point.
+      const float up_f = (tp.bound_mask & 1u) ? __double2float_rd(up) : CUDART_INF_F;
+      const float lo_f = (tp.bound_mask & 2u) ? __double2float_ru(lo) : -CUDART_INF_F;
+      unsigned long long m64 = 0;
 #pragma unroll
       for (int j = 0; j < CV; ++j) {
-        const uint32_t v = gl + j * G;
-        const float x[4] = {cq[j].x, cq[j].y, cq[j].z, cq[j].w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint32_t p = 4u * v + k;
-          const bool f = p < nc && ((chk_up && x[k] > up_f) || (chk_lo && x[k] < lo_f));
-          if (f) { if (p < 32u) mlo |= 1u << p; else mhi |= 1u << (p - 32u); }
-        }
+        const uint32_t v = gl + j * G;               // float4 number: points 4v .. 4v+3
+        const uint32_t nib = ((cq[j].x > up_f || cq[j].x < lo_f) ? 1u : 0u) | ((cq[j].y > up_f || cq[j].y < lo_f) ? 2u : 0u) |
+                             ((cq[j].z > up_f || cq[j].z < lo_f) ? 4u : 0u) | ((cq[j].w > up_f || cq[j].w < lo_f) ? 8u : 0u);
+        if (v < 16u) m64 |= (unsigned long long)nib << (4u * v);
       }
+      if (nc < 64u) m64 &= (1ull << nc) - 1ull;
+      mlo = (uint32_t)m64; mhi = (uint32_t)(m64 >> 32);
     }
     mlo = group_or<G>(mlo); mhi = group_or<G>(mhi);
 
