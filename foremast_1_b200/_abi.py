@@ -22,7 +22,7 @@ FM_ST_KW_RUN = 0x40
 FM_ST_DEGENERATE = 0x80
 
 FM_STRAT_CANARY, FM_STRAT_HISTORICAL = 0, 1
-FM_MA_ALL, FM_MA_WINDOW, FM_MODEL_EWMA, FM_MODEL_DOUBLE_EXP = 0, 1, 2, 3
+FM_MA_ALL, FM_MA_WINDOW, FM_MODEL_EWMA, FM_MODEL_DOUBLE_EXP, FM_MODEL_HOLT_WINTERS = 0, 1, 2, 3, 4
 FM_PW_NONE, FM_PW_MANN_WHITE, FM_PW_WILCOXON, FM_PW_KRUSKAL, FM_PW_ALL, FM_PW_ANY, FM_PW_FRIEDMAN = range(7)
 FM_PAIR_HEAD, FM_PAIR_TAIL = 0, 1
 FM_REC_FULL, FM_REC_COMPACT = 0, 1
@@ -46,8 +46,8 @@ class GlobalParams(C.Structure):
                 ("pairwise_mode", C.c_uint32), ("min_mw", C.c_uint32), ("min_wx", C.c_uint32),
                 ("min_kw", C.c_uint32), ("cc_mw", C.c_uint32), ("cc_wx", C.c_uint32),
                 ("pair_rule", C.c_uint32), ("min_anomaly_points", C.c_uint32),
-                ("reserved", C.c_uint32), ("alpha", C.c_double), ("smooth_alpha", C.c_double),
-                ("smooth_beta", C.c_double)]
+                ("season_len", C.c_uint32), ("alpha", C.c_double), ("smooth_alpha", C.c_double),
+                ("smooth_beta", C.c_double), ("smooth_gamma", C.c_double)]
 
 
 class Batch(C.Structure):
@@ -72,6 +72,14 @@ class Timing(C.Structure):
     _fields_ = [("kernel_ms", C.c_float), ("launches", C.c_uint32), ("h2d_ms", C.c_float),
                 ("d2h_ms", C.c_float), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("main_kernel_ms", C.c_float), ("reserved", C.c_uint32)]
+
+
+class PairBatch(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("reserved", C.c_uint32), ("n_pairs", C.c_uint64),
+                ("cur_x", C.c_void_p), ("cur_y", C.c_void_p), ("cur_len", C.c_void_p),
+                ("n_cur", C.c_uint32), ("cur_pitch", C.c_uint32),
+                ("hist_x", C.c_void_p), ("hist_y", C.c_void_p), ("hist_len", C.c_void_p),
+                ("n_hist", C.c_uint32), ("hist_pitch", C.c_uint32), ("metric_type", C.c_void_p)]
 
 
 class CacheStats(C.Structure):
@@ -99,7 +107,11 @@ RANK_AUX = np.dtype([("r2_cur", "<i8"), ("t_mw", "<i8"), ("w2_plus", "<i8"), ("w
 ROLLUP_REC = np.dtype([("n_children", "<u4"), ("n_unhealthy", "<u4"), ("n_unknown", "<u4"),
                        ("severity", "u1"), ("reserved", "u1", (3,))])
 
-assert SERIES_REC.itemsize == 96 and COMPACT_REC.itemsize == 16
+PAIR_REC = np.dtype([("mean_x", "<f8"), ("mean_y", "<f8"), ("var_x", "<f8"), ("var_y", "<f8"), ("cov_xy", "<f8"),
+                     ("d2_max", "<f8"), ("n_anom", "<u4"), ("first_idx", "<u2"), ("verdict", "u1"),
+                     ("status", "u1"), ("anom_mask", "<u8")])
+
+assert SERIES_REC.itemsize == 96 and COMPACT_REC.itemsize == 16 and PAIR_REC.itemsize == 64
 assert RANK_AUX.itemsize == 48 and ROLLUP_REC.itemsize == 16
 
 # metric-type ids of the default table (foremast-brain.yaml:32-73)
@@ -138,6 +150,8 @@ def default_params():
     g.alpha = 0.05
     g.smooth_alpha = 0.3
     g.smooth_beta = 0.1
+    g.smooth_gamma = 0.1
+    g.season_len = 0
     rows = [(2.0, 1), (2.0, 1), (3.0, 1), (10.0, 3), (5.0, 1), (5.0, 1)]
     table = (TypeParams * len(rows))()
     for i, (k, b) in enumerate(rows):

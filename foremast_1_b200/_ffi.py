@@ -31,6 +31,8 @@ SYMBOLS = {
     "fm_cache_configure": (C.c_int32, [C.c_void_p, C.c_uint64]),
     "fm_cache_query": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
     "fm_cache_get_stats": (C.c_int32, [C.c_void_p, C.c_void_p]),
+    "fm_score_pairs": (C.c_int32, [C.c_void_p, C.POINTER(A.PairBatch), C.c_void_p, C.POINTER(A.Timing)]),
+    "fm_score_pairs_device": (C.c_int32, [C.c_void_p, C.POINTER(A.PairBatch), C.c_void_p, C.POINTER(A.Timing)]),
     "fm_pool_create": (C.c_int32, [C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_void_p)]),
     "fm_pool_destroy": (C.c_int32, [C.c_void_p]),
     "fm_pool_size": (C.c_int32, [C.c_void_p]),

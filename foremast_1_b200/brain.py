@@ -139,7 +139,8 @@ _PAIRWISE = {"ALL": A.FM_PW_ALL, "ANY": A.FM_PW_ANY, "MANN_WHITE": A.FM_PW_MANN_
              "FRIEDMAN": A.FM_PW_FRIEDMAN}   # rollover (pod-group) jobs only
 _ALGORITHMS = {"moving_average_all": A.FM_MA_ALL, "moving_average": A.FM_MA_WINDOW,
                "exponential_smoothing": A.FM_MODEL_EWMA,
-               "double_exponential_smoothing": A.FM_MODEL_DOUBLE_EXP}
+               "double_exponential_smoothing": A.FM_MODEL_DOUBLE_EXP,
+               "holt_winters": A.FM_MODEL_HOLT_WINTERS}
 
 
 def params_from_env(env):
@@ -156,6 +157,11 @@ def params_from_env(env):
         raise ValueError(f"unsupported ML_ALGORITHM {algo!r}")
     g.ma_mode = _ALGORITHMS[algo]
     g.ma_window = int(env.get("ML_MOVING_AVERAGE_WINDOW", "0"))
+    g.season_len = int(env.get("ML_SEASON_LENGTH", "1440" if g.ma_mode == A.FM_MODEL_HOLT_WINTERS else "0"))
+    for name, field in (("ML_SMOOTHING_ALPHA", "smooth_alpha"), ("ML_SMOOTHING_BETA", "smooth_beta"),
+                        ("ML_SMOOTHING_GAMMA", "smooth_gamma")):
+        if name in env:
+            setattr(g, field, float(env[name]))
     g.min_hist_points = int(env.get("MIN_HISTORICAL_DATA_POINT_TO_MEASURE", "10"))
     pw = env.get("ML_PAIRWISE_ALGORITHM", "ANY").upper()
     if pw not in _PAIRWISE:

@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 SO = os.path.join(LIBDIR, "libforemast_cuda.so")
-SOURCES = ["fm_api.cu", "fm_kernels.cu", "fm_canary_sort.cu", "fm_canary_count.cu", "fm_canary_elect.cu", "fm_ma.cu", "fm_groups.cu", "fm_decode.cu", "fm_pool.cu"]
+SOURCES = ["fm_api.cu", "fm_kernels.cu", "fm_canary_sort.cu", "fm_canary_count.cu", "fm_canary_elect.cu", "fm_ma.cu", "fm_groups.cu", "fm_decode.cu", "fm_pool.cu", "fm_pairs.cu"]
 HEADERS = ["fm_internal.h", "fm_device.cuh", "fm_canary_common.cuh", "fm_sortnet.cuh", "fm_sort48.cuh", "fm_sort48_net.cuh", "../../include/foremast_cuda.h", "../../include/fm_synth.h"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

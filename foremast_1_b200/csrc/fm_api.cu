@@ -80,7 +80,7 @@ struct fm_ctx {
   FmParamsDev params;
   FmParamsDev* d_params = nullptr;
   // staging for fm_score_batch: two chunk slots
-  Arena in[2], out[2], roll, misc;
+  Arena in[2], out[2], roll, misc, hw;
   RowCache cache;
   cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
   std::vector<cudaEvent_t> kev;    // per-chunk kernel timing events
@@ -288,9 +288,10 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
   if (b->n_cur > FM_MAX_CUR) return fail(c, FM_E_UNSUPPORTED, "n_cur %u > %u", b->n_cur, FM_MAX_CUR);
   if (canary && (uint64_t)b->n_cur + b->n_base > FM_MAX_RANK_N)
     return fail(c, FM_E_UNSUPPORTED, "n_cur + n_base %u > %u", b->n_cur + b->n_base, FM_MAX_RANK_N);
+  const bool holt_winters = c->params.g.ma_mode == FM_MODEL_HOLT_WINTERS;   // general kernel only
   if (!canary && c->force_path != 1 && b->hist && b->n_cur <= 64 && c->params.g.ma_mode == FM_MA_ALL)
     return plan_ma_only(c, b, pl);
-  if (canary && c->force_path != 1 && b->n_cur <= 64 && b->n_base >= 1) {
+  if (canary && c->force_path != 1 && b->n_cur <= 64 && b->n_base >= 1 && !holt_winters) {
     if (c->force_path == 3 && b->n_base <= 2048) return plan_canary_elect(c, b, pl);
     if (c->force_path != 2 && b->n_cur <= 63 && b->n_base <= 2048) return plan_canary_count(c, b, pl);
     if (b->n_base <= 2048) return plan_canary_sort(c, b, pl);
@@ -338,6 +339,12 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
   a.P = c->d_params;
   a.record_kind = b->record_kind;
   a.strategy = b->strategy;
+  if (holt_winters) {   // seasonal state: season_len doubles per resident warp
+    const uint32_t m = c->params.g.season_len;
+    if (m < 2u || m > (1u << 20)) return fail(c, FM_E_INVALID, "FM_MODEL_HOLT_WINTERS needs 2 <= season_len <= 2^20 (got %u)", m);
+    FM_CK(c, c->hw.reserve((size_t)pl->grid * wpc * m * sizeof(double)));
+    a.hw_scratch = static_cast<double*>(c->hw.p);
+  }
   return FM_OK;
 }
 
@@ -388,6 +395,8 @@ uint32_t fm_sizeof(uint32_t which) {
     case 8: return sizeof(fm_timing);
     case 9: return sizeof(fm_synth_desc);
     case 10: return sizeof(fm_cache_stats);
+    case 11: return sizeof(fm_pair_batch);
+    case 12: return sizeof(fm_pair_rec);
     default: return 0;
   }
 }
@@ -407,7 +416,7 @@ int32_t fm_default_params(fm_global_params* g, fm_type_params* table, uint32_t* 
   g->ddof = 0; g->ma_mode = FM_MA_ALL; g->ma_window = 0; g->min_hist_points = 10;
   g->pairwise_mode = FM_PW_ANY; g->min_mw = 20; g->min_wx = 20; g->min_kw = 5;
   g->cc_mw = 1; g->cc_wx = 0; g->pair_rule = FM_PAIR_HEAD; g->min_anomaly_points = 1;
-  g->alpha = 0.05; g->smooth_alpha = 0.3; g->smooth_beta = 0.1;
+  g->alpha = 0.05; g->smooth_alpha = 0.3; g->smooth_beta = 0.1; g->smooth_gamma = 0.1; g->season_len = 0;
   // foremast-brain.yaml:26-73: default, error5xx, error4xx, latency, cpu, memory
   const double k[6] = {2.0, 2.0, 3.0, 10.0, 5.0, 5.0};
   const uint32_t bound[6] = {1, 1, 1, 3, 1, 1};
@@ -492,7 +501,7 @@ int32_t fm_ctx_destroy(fm_ctx* c) {
     if (c->out_free[i]) cudaEventDestroy(c->out_free[i]);
   }
   for (cudaEvent_t e : c->kev) cudaEventDestroy(e);
-  c->roll.release(); c->misc.release(); c->cache.release();
+  c->roll.release(); c->misc.release(); c->hw.release(); c->cache.release();
   if (c->d_params) cudaFree(c->d_params);
   if (c->ev_a) cudaEventDestroy(c->ev_a);
   if (c->ev_b) cudaEventDestroy(c->ev_b);
@@ -508,7 +517,7 @@ int32_t fm_set_params(fm_ctx* c, const fm_global_params* g, const fm_type_params
   if (!c) return FM_E_INVALID;
   if (!g || !table || n_types == 0 || n_types > FM_MAX_TYPES) return fail(c, FM_E_INVALID, "bad params (n_types %u)", n_types);
   if (g->struct_size != sizeof(fm_global_params)) return fail(c, FM_E_INVALID, "fm_global_params.struct_size %u != %zu", g->struct_size, sizeof(fm_global_params));
-  if (g->ddof > 1 || g->ma_mode > FM_MODEL_DOUBLE_EXP || g->pairwise_mode > FM_PW_FRIEDMAN || g->pair_rule > FM_PAIR_TAIL)
+  if (g->ddof > 1 || g->ma_mode > FM_MODEL_HOLT_WINTERS || g->pairwise_mode > FM_PW_FRIEDMAN || g->pair_rule > FM_PAIR_TAIL)
     return fail(c, FM_E_INVALID, "parameter out of range");
   FM_CK(c, cudaSetDevice(c->device));
   c->params.g = *g;
@@ -966,6 +975,7 @@ static int32_t plan_groups(fm_ctx* c, const fm_group_batch* b, FmGArgs* a, int* 
   if (!b || b->struct_size != sizeof(fm_group_batch)) return fail(c, FM_E_INVALID, "bad fm_group_batch");
   if (!b->group_offsets || (!b->cur && b->n_groups)) return fail(c, FM_E_INVALID, "null group_offsets / cur");
   if ((uint64_t)b->n_cur * FM_MAX_GROUPS > FM_MAX_RANK_N) return fail(c, FM_E_UNSUPPORTED, "n_cur %u too long for %u groups", b->n_cur, FM_MAX_GROUPS);
+  if (c->params.g.ma_mode == FM_MODEL_HOLT_WINTERS) return fail(c, FM_E_UNSUPPORTED, "FM_MODEL_HOLT_WINTERS is a series-batch model (no pod-group form)");
   if ((b->cur_pitch & 3u) || (b->hist && (b->hist_pitch & 3u)) || (reinterpret_cast<uintptr_t>(b->hist) & 15u))
     return fail(c, FM_E_INVALID, "rows must be 16-byte aligned with pitch a multiple of 4");
   a->raw_cap = std::max(64u, b->n_cur * FM_MAX_GROUPS);
@@ -1079,6 +1089,90 @@ int32_t fm_score_groups(fm_ctx* c, const fm_group_batch* b, fm_series_rec* out, 
     timing->h2d_bytes = h2d;
     timing->d2h_bytes = G * sizeof(fm_series_rec) + (out_svc ? V * sizeof(fm_rollup_rec) : 0);
   }
+  return FM_OK;
+}
+
+// ---------------------------------------------------------------------------
+static int32_t validate_pairs(fm_ctx* c, const fm_pair_batch* b, const void* out) {
+  if (!b || !out) return fail(c, FM_E_INVALID, "null pair batch or output");
+  if (b->struct_size != sizeof(fm_pair_batch)) return fail(c, FM_E_INVALID, "fm_pair_batch.struct_size %u != %zu", b->struct_size, sizeof(fm_pair_batch));
+  if (b->n_pairs && ((b->n_cur && (!b->cur_x || !b->cur_y)) || (b->n_hist && (!b->hist_x || !b->hist_y))))
+    return fail(c, FM_E_INVALID, "null row pointer");
+  if (b->n_cur > FM_MAX_CUR) return fail(c, FM_E_UNSUPPORTED, "n_cur %u > %u", b->n_cur, FM_MAX_CUR);
+  auto bad = [](const float* p, uint32_t n, uint32_t pitch) {
+    return p && ((reinterpret_cast<uintptr_t>(p) & 15u) || (pitch & 3u) || pitch < ((n + 3u) & ~3u));
+  };
+  if (bad(b->cur_x, b->n_cur, b->cur_pitch) || bad(b->cur_y, b->n_cur, b->cur_pitch) ||
+      bad(b->hist_x, b->n_hist, b->hist_pitch) || bad(b->hist_y, b->n_hist, b->hist_pitch))
+    return fail(c, FM_E_INVALID, "rows must be 16-byte aligned with pitch a multiple of 4 and >= roundup4(n)");
+  return FM_OK;
+}
+
+int32_t fm_score_pairs_device(fm_ctx* c, const fm_pair_batch* b, fm_pair_rec* d_out, fm_timing* timing) {
+  if (!c) return FM_E_INVALID;
+  int32_t rc = validate_pairs(c, b, d_out);
+  if (rc != FM_OK) return rc;
+  FM_CK(c, cudaSetDevice(c->device));
+  if (timing) memset(timing, 0, sizeof(*timing));
+  if (b->n_pairs == 0) return FM_OK;
+  if (timing) FM_CK(c, cudaEventRecord(c->ev_a, c->stream));
+  const uint32_t launches = (uint32_t)fm_launch_pairs(*b, c->d_params, d_out, c->num_sms, c->stream);
+  FM_CK(c, cudaGetLastError());
+  if (timing) {
+    FM_CK(c, cudaEventRecord(c->ev_b, c->stream));
+    FM_CK(c, cudaEventSynchronize(c->ev_b));
+    FM_CK(c, cudaEventElapsedTime(&timing->kernel_ms, c->ev_a, c->ev_b));
+    timing->main_kernel_ms = timing->kernel_ms;
+    timing->launches = launches;
+  }
+  return FM_OK;
+}
+
+int32_t fm_score_pairs(fm_ctx* c, const fm_pair_batch* b, fm_pair_rec* out, fm_timing* timing) {
+  if (!c) return FM_E_INVALID;
+  int32_t rc = validate_pairs(c, b, out);
+  if (rc != FM_OK) return rc;
+  FM_CK(c, cudaSetDevice(c->device));
+  if (timing) memset(timing, 0, sizeof(*timing));
+  const uint64_t P = b->n_pairs;
+  if (P == 0) return FM_OK;
+  auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
+  const size_t cb = al(P * b->cur_pitch * 4), hb = al(P * b->hist_pitch * 4);
+  size_t o = 0;
+  const size_t o_cx = o; o += cb;
+  const size_t o_cy = o; o += cb;
+  const size_t o_hx = o; o += hb;
+  const size_t o_hy = o; o += hb;
+  const size_t o_cl = o; o += b->cur_len ? al(P * 4) : 0;
+  const size_t o_hl = o; o += b->hist_len ? al(P * 4) : 0;
+  const size_t o_mt = o; o += b->metric_type ? al(P) : 0;
+  FM_CK(c, c->in[0].reserve(o));
+  FM_CK(c, c->out[0].reserve(al(P * sizeof(fm_pair_rec))));
+  char* din = static_cast<char*>(c->in[0].p);
+  uint64_t h2d = 0;
+  auto up = [&](size_t off, const void* src, size_t bytes) -> cudaError_t {
+    h2d += bytes;
+    return bytes ? cudaMemcpyAsync(din + off, src, bytes, cudaMemcpyHostToDevice, c->stream) : cudaSuccess;
+  };
+  FM_CK(c, up(o_cx, b->cur_x, P * b->cur_pitch * 4));
+  FM_CK(c, up(o_cy, b->cur_y, P * b->cur_pitch * 4));
+  FM_CK(c, up(o_hx, b->hist_x, P * b->hist_pitch * 4));
+  FM_CK(c, up(o_hy, b->hist_y, P * b->hist_pitch * 4));
+  if (b->cur_len) FM_CK(c, up(o_cl, b->cur_len, P * 4));
+  if (b->hist_len) FM_CK(c, up(o_hl, b->hist_len, P * 4));
+  if (b->metric_type) FM_CK(c, up(o_mt, b->metric_type, P));
+  fm_pair_batch db = *b;
+  db.cur_x = reinterpret_cast<const float*>(din + o_cx); db.cur_y = reinterpret_cast<const float*>(din + o_cy);
+  db.hist_x = reinterpret_cast<const float*>(din + o_hx); db.hist_y = reinterpret_cast<const float*>(din + o_hy);
+  db.cur_len = b->cur_len ? reinterpret_cast<const uint32_t*>(din + o_cl) : nullptr;
+  db.hist_len = b->hist_len ? reinterpret_cast<const uint32_t*>(din + o_hl) : nullptr;
+  db.metric_type = b->metric_type ? reinterpret_cast<const uint8_t*>(din + o_mt) : nullptr;
+  fm_timing t; memset(&t, 0, sizeof(t));
+  rc = fm_score_pairs_device(c, &db, static_cast<fm_pair_rec*>(c->out[0].p), &t);
+  if (rc != FM_OK) { cudaStreamSynchronize(c->stream); return rc; }
+  FM_CK(c, cudaMemcpyAsync(out, c->out[0].p, P * sizeof(fm_pair_rec), cudaMemcpyDeviceToHost, c->stream));
+  FM_CK(c, cudaStreamSynchronize(c->stream));
+  if (timing) { *timing = t; timing->h2d_bytes = h2d; timing->d2h_bytes = P * sizeof(fm_pair_rec); }
   return FM_OK;
 }
 

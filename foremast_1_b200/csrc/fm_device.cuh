@@ -307,13 +307,64 @@ __device__ __forceinline__ void fm_model_smoothing(const fm_global_params& g, co
   sigma = (steps > g.ddof) ? sqrt(sse / (double)(steps - g.ddof)) : 0.0;
 }
 
+// Additive Holt-Winters (design.md:60-66), A.2c: season of m points, level / trend / seasonal
+// factors smooth_alpha / smooth_beta / smooth_gamma.  Start: level = mean of the first season,
+// trend = (mean of the second season - level) / m, season_i = x_i - level.  From t = m on:
+//   f = level + trend + season[t mod m]  (one-step-ahead forecast; its errors give sigma),
+//   level' = a (x_t - season) + (1-a)(level + trend), trend' = b (level' - level) + (1-b) trend,
+//   season[t mod m]' = c (x_t - level') + (1-c) season.
+// The recurrence rewrites a different seasonal slot at every step, so it is not a fixed linear
+// map that a scan could compose: lane 0 runs it, the seasonal state lives in `season` (m doubles
+// of global scratch per warp), the two start sums and everything after the recurrence use the
+// whole warp.  Centre of current point i (0-based): level + (i+1) trend + season[(n+i) mod m];
+// `c1` is the centre of point 0, `hw` carries what fm_threshold_hw needs for the others.
+struct FmHw { double trend; const double* season; uint32_t n, m; };
+
+__device__ __forceinline__ bool fm_model_hw(const fm_global_params& g, const float* x, uint32_t n, int lane,
+                                            double* season, double& c1, double& sigma, FmHw& hw) {
+  const uint32_t m = g.season_len;
+  const uint32_t need = max(g.min_hist_points, g.ddof + 1u);
+  c1 = 0.0; sigma = 0.0;
+  hw.trend = 0.0; hw.season = season; hw.n = n; hw.m = m;
+  if (x == nullptr || season == nullptr || m < 2u || n < 2u * m || n < need) return false;
+  double sa = 0.0, sb = 0.0;
+  for (uint32_t i = lane; i < m; i += 32) { sa += (double)x[i]; sb += (double)x[m + i]; }
+  sa = fm_warp_sum(sa); sb = fm_warp_sum(sb);
+  double level = sa / (double)m;
+  double trend = (sb / (double)m - level) / (double)m;
+  for (uint32_t i = lane; i < m; i += 32) season[i] = (double)x[i] - level;
+  __syncwarp();
+  double sse = 0.0;
+  if (lane == 0) {
+    const double a = g.smooth_alpha, b = g.smooth_beta, c = g.smooth_gamma;
+    uint32_t slot = 0;                                  // t mod m, t starts at m
+    for (uint32_t t = m; t < n; ++t) {
+      const double xt = (double)x[t], si = season[slot];
+      const double e = xt - (level + trend + si);
+      sse = fma(e, e, sse);
+      const double nl = a * (xt - si) + (1.0 - a) * (level + trend);
+      trend = b * (nl - level) + (1.0 - b) * trend;
+      season[slot] = c * (xt - nl) + (1.0 - c) * si;
+      level = nl;
+      if (++slot == m) slot = 0;
+    }
+  }
+  __syncwarp();
+  level = __shfl_sync(FM_FULL, level, 0); trend = __shfl_sync(FM_FULL, trend, 0); sse = __shfl_sync(FM_FULL, sse, 0);
+  const uint32_t cnt = n - m;
+  hw.trend = trend;
+  c1 = level + trend + season[n % m];
+  sigma = cnt > g.ddof ? sqrt(sse / (double)(cnt - g.ddof)) : 0.0;
+  return true;
+}
+
 // a2: model window -> (mean, sigma).  `x` global or shared; `vec_ok` = row is a
 // 16-byte aligned global row.  Returns false when the window is too short.
 __device__ __forceinline__ bool fm_model(const fm_global_params& g, const float* x, uint32_t n,
                                          bool vec_ok, int lane, double& mean, double& sigma) {
   uint32_t need = max(g.min_hist_points, g.ddof + 1u);
   mean = 0.0; sigma = 0.0;
-  if (x == nullptr) return false;
+  if (x == nullptr || g.ma_mode == FM_MODEL_HOLT_WINTERS) return false;   // Holt-Winters: fm_model_hw, general kernel
   if (g.ma_mode == FM_MA_WINDOW) {
     const uint32_t w = g.ma_window;
     need = max(need, w);
@@ -519,6 +570,41 @@ __device__ __forceinline__ void fm_threshold(const fm_global_params& g, const fm
     bool a = false;
     if (i < n_cur) {
       const double x = (double)cur[i];
+      a = ((tp.bound_mask & 1u) && x > up) || ((tp.bound_mask & 2u) && x < lo);
+    }
+    const uint32_t b = __ballot_sync(FM_FULL, a);
+    if (b) {
+      if (first == 0xFFFFFFFFu) first = i0 + (uint32_t)__ffs((int)b) - 1u;
+      cnt += (uint32_t)__popc(b);
+      if (i0 < 64) mask |= (uint64_t)b << i0;
+    }
+  }
+  rec.n_anom = cnt;
+  rec.first_idx = (uint16_t)(first == 0xFFFFFFFFu ? 0xFFFFu : (first < 0xFFFFu ? first : 0xFFFEu));
+  rec.anom_mask = mask;
+  rec.verdict = (cnt >= g.min_anomaly_points && cnt > 0) ? FM_UNHEALTHY : FM_HEALTHY;
+}
+
+// A.7 + A.8 for a seasonal model: current point i is compared after its own centre has been moved
+// onto the first one's, x_i - (centre_i - centre_0) against centre_0 +- k sigma (rec.upper / lower
+// are the bounds of point 0; point i's are those plus the same offset).
+__device__ __forceinline__ void fm_threshold_hw(const fm_global_params& g, const fm_type_params& tp,
+                                                bool differ, const float* cur, uint32_t n_cur, int lane,
+                                                const FmHw& hw, fm_series_rec& rec) {
+  const double k = differ ? tp.k_low : tp.k;
+  const double up = __dadd_rn(rec.mean, __dmul_rn(k, rec.sigma));
+  double lo = __dsub_rn(rec.mean, __dmul_rn(k, rec.sigma));
+  if (lo < tp.min_lower_bound) lo = tp.min_lower_bound;
+  rec.upper = up; rec.lower = lo;
+  const double s0 = hw.season[hw.n % hw.m];
+  uint32_t cnt = 0, first = 0xFFFFFFFFu;
+  uint64_t mask = 0;
+  for (uint32_t i0 = 0; i0 < n_cur; i0 += 32) {
+    const uint32_t i = i0 + lane;
+    bool a = false;
+    if (i < n_cur) {
+      const double off = __dadd_rn(__dmul_rn((double)i, hw.trend), __dsub_rn(hw.season[(hw.n + i) % hw.m], s0));
+      const double x = __dsub_rn((double)cur[i], off);
       a = ((tp.bound_mask & 1u) && x > up) || ((tp.bound_mask & 2u) && x < lo);
     }
     const uint32_t b = __ballot_sync(FM_FULL, a);

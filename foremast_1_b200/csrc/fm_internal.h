@@ -37,6 +37,7 @@ struct FmKArgs {
   uint32_t warp_bytes;     // bytes of shared memory per warp
   uint32_t log_m;          // k_canary_elect: log2 of the election table size; k_canary_count: its slot count
   uint32_t cnt_nv, cnt_ns; // k_canary_count: vector rows / scalar rows of the staged baseline per lane
+  double* hw_scratch;      // k_score_series, Holt-Winters: season_len doubles per resident warp
 };
 
 struct FmGArgs {
@@ -84,6 +85,9 @@ int fm_launch_ma_window(const float* d_x, uint32_t n, uint32_t w, uint32_t ddof,
                         double* d_p2, double* d_mean, double* d_sigma, cudaStream_t st);
 int fm_launch_synth(const fm_synth_desc& d, float* cur, float* base, float* hist, uint8_t* mt,
                     cudaStream_t st);
+
+// fm_pairs.cu
+int fm_launch_pairs(const fm_pair_batch& b, const FmParamsDev* P, fm_pair_rec* out, int num_sms, cudaStream_t st);
 
 // message for fm_last_error(NULL) of the calling thread (entry points that take no ctx)
 void fm_set_thread_error(const char* fmt, ...);

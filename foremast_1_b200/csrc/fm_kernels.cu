@@ -116,7 +116,13 @@ __global__ void __launch_bounds__(512) k_score_series(const FmKArgs a) {
 
     // ---- a2: model window ------------------------------------------------
     bool model_ok;
-    if (a.hist) {
+    const bool holt_winters = g.ma_mode == FM_MODEL_HOLT_WINTERS;
+    FmHw hw = {0.0, nullptr, 0u, 0u};
+    if (holt_winters) {
+      double* season = a.hw_scratch ? a.hw_scratch + ((uint64_t)blockIdx.x * wpc + warp) * g.season_len : nullptr;
+      if (a.hist) model_ok = fm_model_hw(g, a.hist + s * a.hist_pitch, row_len(a.hist_len, s, a.n_hist), lane, season, rec.mean, rec.sigma, hw);
+      else model_ok = fm_model_hw(g, canary ? base : nullptr, nb, lane, season, rec.mean, rec.sigma, hw);
+    } else if (a.hist) {
       const uint32_t nh = row_len(a.hist_len, s, a.n_hist);
       model_ok = fm_model(g, a.hist + s * a.hist_pitch, nh, true, lane, rec.mean, rec.sigma);
     } else {
@@ -225,7 +231,10 @@ __global__ void __launch_bounds__(512) k_score_series(const FmKArgs a) {
     }
 
     // ---- a7, a8 -----------------------------------------------------------
-    if (model_ok && nc > 0) fm_threshold(g, tp, differ, cur, nc, lane, rec);
+    if (model_ok && nc > 0) {
+      if (holt_winters) fm_threshold_hw(g, tp, differ, cur, nc, lane, hw, rec);
+      else fm_threshold(g, tp, differ, cur, nc, lane, rec);
+    }
     if (status & (FM_ST_NO_CURRENT | FM_ST_HIST_INSUFFICIENT)) rec.verdict = FM_UNKNOWN;
     rec.status = (uint8_t)status;
 

@@ -190,6 +190,28 @@ class Context:
         self._ck(self._lib.fm_score_groups(self._h, C.byref(b), A.ptr(rec), A.ptr(svc), C.byref(t)))
         return {"rec": rec, "svc": svc, "timing": t, "batch": b, "_keep": [cur, hist, off, cl, hl, mt]}
 
+    def score_pairs(self, cur_x, cur_y, hist_x, hist_y, *, cur_len=None, hist_len=None, metric_type=None):
+        """Two metrics judged jointly (bivariate normal, fm_score_pairs): rows of pair p are
+        cur_x[p], cur_y[p], hist_x[p], hist_y[p]."""
+        cx, n_cur = _as_matrix(cur_x)
+        cy, _ = _as_matrix(cur_y)
+        hx, n_hist = _as_matrix(hist_x)
+        hy, _ = _as_matrix(hist_y)
+        P = cx.shape[0]
+        b = A.PairBatch()
+        b.struct_size = C.sizeof(A.PairBatch)
+        b.n_pairs = P
+        b.cur_x, b.cur_y, b.n_cur, b.cur_pitch = A.ptr(cx), A.ptr(cy), n_cur, cx.shape[1]
+        b.hist_x, b.hist_y, b.n_hist, b.hist_pitch = A.ptr(hx), A.ptr(hy), n_hist, hx.shape[1]
+        cl = None if cur_len is None else np.ascontiguousarray(cur_len, dtype=np.uint32)
+        hl = None if hist_len is None else np.ascontiguousarray(hist_len, dtype=np.uint32)
+        mt = None if metric_type is None else np.ascontiguousarray(metric_type, dtype=np.uint8)
+        b.cur_len, b.hist_len, b.metric_type = A.ptr(cl), A.ptr(hl), A.ptr(mt)
+        rec = np.zeros(P, A.PAIR_REC)
+        t = A.Timing()
+        self._ck(self._lib.fm_score_pairs(self._h, C.byref(b), A.ptr(rec), C.byref(t)))
+        return {"rec": rec, "timing": t, "batch": b, "_keep": [cx, cy, hx, hy, cl, hl, mt]}
+
     def rank_dump(self, cur, base):
         cur = np.ascontiguousarray(cur, dtype=np.float32)
         base = np.ascontiguousarray(base, dtype=np.float32)

@@ -74,6 +74,9 @@ extern "C" {
 #define FM_MA_WINDOW  1u  /* trailing window of ma_window points                      */
 #define FM_MODEL_EWMA        2u /* exponential smoothing (design.md:60-66)            */
 #define FM_MODEL_DOUBLE_EXP  3u /* double exponential smoothing (Holt linear)         */
+#define FM_MODEL_HOLT_WINTERS 4u /* additive Holt-Winters, season of season_len points
+                                  (design.md:60-66); series batches only, scored by
+                                  the general kernel                                  */
 
 /* ---- pairwise mode (foremast-brain/README.md:34) ----------------------- */
 #define FM_PW_NONE       0u
@@ -126,10 +129,11 @@ typedef struct {
   uint32_t cc_mw, cc_wx;       /* continuity correction on/off (1 / 0)     */
   uint32_t pair_rule;          /* FM_PAIR_HEAD / FM_PAIR_TAIL              */
   uint32_t min_anomaly_points; /* default 1 (fail fast, design.md:43)      */
-  uint32_t reserved;
+  uint32_t season_len;         /* FM_MODEL_HOLT_WINTERS: points per season (>= 2) */
   double   alpha;              /* ML_PAIRWISE_THRESHOLD, default 0.05      */
   double   smooth_alpha;       /* level factor for FM_MODEL_EWMA/DOUBLE_EXP */
-  double   smooth_beta;        /* trend factor for FM_MODEL_DOUBLE_EXP      */
+  double   smooth_beta;        /* trend factor for FM_MODEL_DOUBLE_EXP / HOLT_WINTERS */
+  double   smooth_gamma;       /* seasonal factor for FM_MODEL_HOLT_WINTERS  */
 } fm_global_params;
 
 /* Full per-series result, 96 B.  U1/W are exact half-integers; p-values and
@@ -314,6 +318,36 @@ int32_t fm_score_batch_cached(fm_ctx* ctx, const fm_batch* batch, const uint64_t
                               fm_rollup_rec* out_svc, fm_timing* timing);
 int32_t fm_cache_query(fm_ctx* ctx, const uint64_t* row_ids, uint64_t n, uint8_t* resident_out);
 int32_t fm_cache_get_stats(fm_ctx* ctx, fm_cache_stats* out);
+
+/* Two metrics of one job judged jointly: "Two Metrics — Bivariate Normal
+ * Distribution" (docs/guides/design.md:67-76).  From the historical pairs
+ * (hist_x[t], hist_y[t]) the means and the 2 x 2 covariance matrix (ddof of the
+ * global params); a current pair is anomalous when its squared Mahalanobis
+ * distance exceeds k^2, k = the threshold of the pair's metric type (rule A.2d in
+ * DESIGN.md).  Fewer than max(min_hist_points, ddof + 1, 3) pairs -> unknown
+ * (FM_ST_HIST_INSUFFICIENT); a singular covariance (constant or collinear
+ * history: det <= 1e-9 var_x var_y) -> unknown (FM_ST_DEGENERATE).  Rows: 16-byte aligned, pitch a
+ * multiple of 4, the two rows of a pair share their lengths. */
+typedef struct {
+  uint32_t struct_size;
+  uint32_t reserved;
+  uint64_t n_pairs;
+  const float* cur_x;  const float* cur_y;  const uint32_t* cur_len;  uint32_t n_cur;  uint32_t cur_pitch;
+  const float* hist_x; const float* hist_y; const uint32_t* hist_len; uint32_t n_hist; uint32_t hist_pitch;
+  const uint8_t* metric_type;     /* [n_pairs], NULL = type 0 */
+} fm_pair_batch;
+
+typedef struct {
+  double   mean_x, mean_y, var_x, var_y, cov_xy;
+  double   d2_max;          /* largest squared Mahalanobis distance of a current pair */
+  uint32_t n_anom;
+  uint16_t first_idx;       /* 0xFFFF if none */
+  uint8_t  verdict, status;
+  uint64_t anom_mask;       /* first 64 current pairs */
+} fm_pair_rec;
+
+int32_t fm_score_pairs(fm_ctx* ctx, const fm_pair_batch* batch, fm_pair_rec* out, fm_timing* timing);
+int32_t fm_score_pairs_device(fm_ctx* ctx, const fm_pair_batch* batch, fm_pair_rec* d_out, fm_timing* timing);
 
 /* Several GPUs from ONE process (one host thread and one ctx per
  * GPU, results gathered into one pinned array; the shared-nothing brain nodes of

@@ -251,6 +251,7 @@ static void fmo_threshold(const fm_global_params* g, const fm_type_params* tp, i
 static int fmo_model(const fm_global_params* g, const float* x, uint32_t n, double* mean, double* sigma) {
   uint32_t need = g->min_hist_points > g->ddof + 1 ? g->min_hist_points : g->ddof + 1;
   *mean = 0.0; *sigma = 0.0;
+  if (g->ma_mode == FM_MODEL_HOLT_WINTERS) return 0;   /* series batches only: fmo_model_hw */
   if (g->ma_mode == FM_MA_WINDOW) {
     const uint32_t w = g->ma_window;
     if (w > need) need = w;
@@ -283,6 +284,68 @@ static int fmo_model(const fm_global_params* g, const float* x, uint32_t n, doub
   return 1;
 }
 
+/* A.2c additive Holt-Winters (docs/guides/design.md:60-66 lists it; the recurrence is the
+ * textbook one, declared in DESIGN.md section 3): season of m points; level = mean of the first
+ * season, trend = (mean of the second season - level) / m, season_i = x_i - level; from t = m on the
+ * one-step-ahead forecast level + trend + season[t mod m], its error, and the three updates.
+ * Returns 0 when the window is shorter than two seasons.  season: m doubles, left holding the
+ * final seasonal state (the caller frees it). */
+static int fmo_model_hw(const fm_global_params* g, const float* x, uint32_t n, double* season,
+                        double* c1, double* sigma, double* trend_out) {
+  const uint32_t m = g->season_len;
+  const uint32_t need = g->min_hist_points > g->ddof + 1 ? g->min_hist_points : g->ddof + 1;
+  *c1 = 0.0; *sigma = 0.0; *trend_out = 0.0;
+  if (m < 2 || n < 2 * m || n < need) return 0;
+  double sa = 0.0, sb = 0.0;
+  for (uint32_t i = 0; i < m; ++i) { sa += (double)x[i]; sb += (double)x[m + i]; }
+  double level = sa / (double)m;
+  double trend = (sb / (double)m - level) / (double)m;
+  for (uint32_t i = 0; i < m; ++i) season[i] = (double)x[i] - level;
+  const double a = g->smooth_alpha, b = g->smooth_beta, c = g->smooth_gamma;
+  double sse = 0.0;
+  for (uint32_t t = m; t < n; ++t) {
+    const uint32_t slot = t % m;
+    const double xt = (double)x[t], si = season[slot];
+    const double e = xt - (level + trend + si);
+    sse += e * e;
+    const double nl = a * (xt - si) + (1.0 - a) * (level + trend);
+    trend = b * (nl - level) + (1.0 - b) * trend;
+    season[slot] = c * (xt - nl) + (1.0 - c) * si;
+    level = nl;
+  }
+  const uint32_t cnt = n - m;
+  *trend_out = trend;
+  *c1 = level + trend + season[n % m];
+  *sigma = cnt > g->ddof ? sqrt(sse / (double)(cnt - g->ddof)) : 0.0;
+  return 1;
+}
+
+/* A.7 + A.8 for the seasonal model: point i is compared after its own centre has been moved onto
+ * the first one's: x_i - (centre_i - centre_0) against centre_0 +- k sigma. */
+static void fmo_threshold_hw(const fm_global_params* g, const fm_type_params* tp, int differ,
+                             const float* cur, uint32_t n_cur, const double* season, uint32_t n, uint32_t m,
+                             double trend, fm_series_rec* rec) {
+  const double k = differ ? tp->k_low : tp->k;
+  const double up = rec->mean + k * rec->sigma;
+  double lo = rec->mean - k * rec->sigma;
+  if (lo < tp->min_lower_bound) lo = tp->min_lower_bound;
+  rec->upper = up; rec->lower = lo;
+  const double s0 = season[n % m];
+  uint32_t n_anom = 0; uint16_t first = 0xFFFFu; uint64_t mask = 0;
+  for (uint32_t i = 0; i < n_cur; ++i) {
+    const double off = (double)i * trend + (season[(n + i) % m] - s0);
+    const double x = (double)cur[i] - off;
+    const int a = ((tp->bound_mask & 1u) && x > up) || ((tp->bound_mask & 2u) && x < lo);
+    if (a) {
+      if (n_anom == 0) first = (uint16_t)(i < 0xFFFFu ? i : 0xFFFEu);
+      ++n_anom;
+      if (i < 64) mask |= 1ull << i;
+    }
+  }
+  rec->n_anom = n_anom; rec->first_idx = first; rec->anom_mask = mask;
+  rec->verdict = (n_anom >= g->min_anomaly_points && n_anom > 0) ? FM_UNHEALTHY : FM_HEALTHY;
+}
+
 static void fmo_score_series_ws(fmo_ws* ws, const fm_global_params* g, const fm_type_params* tp,
                                 uint32_t strategy, const float* cur, uint32_t n_cur,
                                 const float* base, uint32_t n_base, const float* hist,
@@ -299,7 +362,15 @@ static void fmo_score_series_ws(fmo_ws* ws, const fm_global_params* g, const fm_
    * historical row is sent (n_hist' = 0 in config 3). */
   const float* mx = hist ? hist : base;
   const uint32_t mn = hist ? n_hist : n_base;
-  const int model_ok = mx ? fmo_model(g, mx, mn, &rec->mean, &rec->sigma) : 0;
+  const int holt_winters = g->ma_mode == FM_MODEL_HOLT_WINTERS;
+  double* season = NULL; double hw_trend = 0.0;
+  int model_ok;
+  if (holt_winters) {
+    season = (g->season_len >= 2 && g->season_len <= (1u << 20)) ? (double*)malloc((size_t)g->season_len * sizeof(double)) : NULL;
+    model_ok = (mx && season) ? fmo_model_hw(g, mx, mn, season, &rec->mean, &rec->sigma, &hw_trend) : 0;
+  } else {
+    model_ok = mx ? fmo_model(g, mx, mn, &rec->mean, &rec->sigma) : 0;
+  }
   if (!model_ok) status |= FM_ST_HIST_INSUFFICIENT;
   if (n_cur == 0) status |= FM_ST_NO_CURRENT;
 
@@ -367,7 +438,11 @@ static void fmo_score_series_ws(fmo_ws* ws, const fm_global_params* g, const fm_
   }
 
   /* a7, a8 */
-  if (model_ok && n_cur > 0) fmo_threshold(g, tp, differ, cur, n_cur, rec);
+  if (model_ok && n_cur > 0) {
+    if (holt_winters) fmo_threshold_hw(g, tp, differ, cur, n_cur, season, mn, g->season_len, hw_trend, rec);
+    else fmo_threshold(g, tp, differ, cur, n_cur, rec);
+  }
+  free(season);
   if ((status & (FM_ST_NO_CURRENT | FM_ST_HIST_INSUFFICIENT)) != 0) rec->verdict = FM_UNKNOWN;
   rec->status = (uint8_t)status;
   if (aux) *aux = ax;
@@ -655,4 +730,61 @@ int32_t fmo_bench_synth(const fm_global_params* g, const fm_type_params* table, 
   free(th); free(jobs);
   *seconds = mx; if (checksum) *checksum = sum;
   return FM_OK;
+}
+
+/* A.2d: two metrics judged jointly, "Bivariate Normal Distribution" (docs/guides/design.md:67-76).
+ * Two-pass means and covariances (ddof of g), squared Mahalanobis distance of every current pair
+ * against k^2. */
+int32_t fmo_score_pairs(const fm_global_params* g, const fm_type_params* table, uint32_t n_types,
+                        const fm_pair_batch* b, fm_pair_rec* out) {
+  uint32_t need = g->min_hist_points > g->ddof + 1 ? g->min_hist_points : g->ddof + 1;
+  if (need < 3) need = 3;
+  for (uint64_t s = 0; s < b->n_pairs; ++s) {
+    fm_pair_rec r; memset(&r, 0, sizeof(r));
+    r.first_idx = 0xFFFFu;
+    const uint32_t nh = fmo_len(b->hist_len, s, b->n_hist), nc = fmo_len(b->cur_len, s, b->n_cur);
+    const float* hx = b->hist_x + s * b->hist_pitch; const float* hy = b->hist_y + s * b->hist_pitch;
+    uint32_t status = 0;
+    if (nc == 0) status |= FM_ST_NO_CURRENT;
+    int ok = nh >= need;
+    double det = 0.0;
+    if (ok) {
+      double mx = 0.0, my = 0.0;
+      for (uint32_t t = 0; t < nh; ++t) { mx += (double)hx[t]; my += (double)hy[t]; }
+      mx /= (double)nh; my /= (double)nh;
+      double vx = 0.0, vy = 0.0, cv = 0.0;
+      for (uint32_t t = 0; t < nh; ++t) {
+        const double dx = (double)hx[t] - mx, dy = (double)hy[t] - my;
+        vx += dx * dx; vy += dy * dy; cv += dx * dy;
+      }
+      const double dd = (double)(nh - g->ddof);
+      r.mean_x = mx; r.mean_y = my; r.var_x = vx / dd; r.var_y = vy / dd; r.cov_xy = cv / dd;
+      det = r.var_x * r.var_y - r.cov_xy * r.cov_xy;
+      if (!(det > 1e-9 * r.var_x * r.var_y)) { status |= FM_ST_DEGENERATE; ok = 0; }   /* 1 - rho^2 <= 1e-9 */
+    } else {
+      status |= FM_ST_HIST_INSUFFICIENT;
+    }
+    if (ok && nc > 0) {
+      const uint32_t ty = b->metric_type ? b->metric_type[s] : 0;
+      const double k = table[ty < n_types ? ty : 0].k, k2 = k * k;
+      const float* cx = b->cur_x + s * b->cur_pitch; const float* cy = b->cur_y + s * b->cur_pitch;
+      uint32_t n_anom = 0; uint64_t mask = 0; double dmax = 0.0;
+      for (uint32_t i = 0; i < nc; ++i) {
+        const double dx = (double)cx[i] - r.mean_x, dy = (double)cy[i] - r.mean_y;
+        const double d2 = (r.var_y * dx * dx - 2.0 * r.cov_xy * dx * dy + r.var_x * dy * dy) / det;
+        if (d2 > dmax) dmax = d2;
+        if (d2 > k2) {
+          if (n_anom == 0) r.first_idx = (uint16_t)(i < 0xFFFFu ? i : 0xFFFEu);
+          ++n_anom;
+          if (i < 64) mask |= 1ull << i;
+        }
+      }
+      r.d2_max = dmax; r.n_anom = n_anom; r.anom_mask = mask;
+      r.verdict = (n_anom >= g->min_anomaly_points && n_anom > 0) ? FM_UNHEALTHY : FM_HEALTHY;
+    }
+    if (status & (FM_ST_NO_CURRENT | FM_ST_HIST_INSUFFICIENT | FM_ST_DEGENERATE)) r.verdict = FM_UNKNOWN;
+    r.status = (uint8_t)status;
+    out[s] = r;
+  }
+  return 0;
 }

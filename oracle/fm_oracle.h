@@ -79,4 +79,8 @@ int32_t fmo_bench_synth(const fm_global_params* g, const fm_type_params* table, 
 #ifdef __cplusplus
 }
 #endif
+/* A.2d: bivariate normal over metric pairs (docs/guides/design.md:67-76). */
+int32_t fmo_score_pairs(const fm_global_params* g, const fm_type_params* table, uint32_t n_types,
+                        const fm_pair_batch* b, fm_pair_rec* out);
+
 #endif

@@ -111,6 +111,14 @@ def score_batch(g, table, batch, n_threads=4, want_aux=True):
     return {"rec": rec, "aux": aux, "api": api, "svc": svc}
 
 
+def score_pairs(g, table, pbatch):
+    """pbatch: a _abi.PairBatch with HOST pointers -> PAIR_REC array."""
+    rec = np.zeros(int(pbatch.n_pairs), A.PAIR_REC)
+    rc = lib().fmo_score_pairs(C.byref(g), table, C.c_uint32(len(table)), C.byref(pbatch), C.c_void_p(rec.ctypes.data))
+    assert rc == 0, rc
+    return rec
+
+
 def score_groups(g, table, gbatch, n_threads=4):
     rec = np.zeros(int(gbatch.n_groups), A.SERIES_REC)
     svc = np.zeros(int(gbatch.n_services), A.ROLLUP_REC)

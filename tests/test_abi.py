@@ -33,8 +33,9 @@ def test_struct_sizes_match_compiled_library():
     lib = _ffi.lib()
     mirror = [C.sizeof(A.GlobalParams), C.sizeof(A.TypeParams), C.sizeof(A.Batch), C.sizeof(A.GroupBatch),
               A.SERIES_REC.itemsize, A.COMPACT_REC.itemsize, A.RANK_AUX.itemsize, A.ROLLUP_REC.itemsize,
-              C.sizeof(A.Timing), C.sizeof(A.SynthDesc), C.sizeof(A.CacheStats)]
-    assert [lib.fm_sizeof(i) for i in range(11)] == mirror
+              C.sizeof(A.Timing), C.sizeof(A.SynthDesc), C.sizeof(A.CacheStats), C.sizeof(A.PairBatch),
+              A.PAIR_REC.itemsize]
+    assert [lib.fm_sizeof(i) for i in range(13)] == mirror
     assert lib.fm_sizeof(99) == 0
     assert lib.fm_version() == (0 << 16) | 1
 

@@ -367,6 +367,75 @@ def test_smoothing_models_scan(ctx, mode, nh):
              metric_type=rng.integers(0, 6, S).astype(np.uint8))
 
 
+@pytest.mark.parametrize("m,nh", [(2, 4), (2, 5), (7, 14), (24, 100), (60, 1440), (1440, 10080)])
+def test_holt_winters(ctx, m, nh):
+    """Additive Holt-Winters (docs/guides/design.md:60-66; A.2c) against the oracle's sequential
+    recurrence: centre of every current point, sigma, per-point flags; ragged histories (shorter
+    than two seasons -> unknown), a trend, a level shift, as the model of a canary batch too."""
+    rng = np.random.default_rng(900 + m + nh)
+    S = 40
+    t = np.arange(nh + 64, dtype=np.float64)
+    wave = 50 + 0.002 * t[None, :] * rng.normal(1, 1, (S, 1)) + 8 * np.sin(2 * np.pi * t[None, :] / m + rng.uniform(0, 6, (S, 1)))
+    x = (wave + rng.normal(0, 0.5, (S, nh + 64))).astype(np.float32)
+    hist = x[:, :nh].copy()
+    hist[: S // 4, nh // 2:] += 5.0
+    cur = x[:, nh: nh + 40].copy()
+    cur[::5, 7] += 12.0                                     # a spike the seasonal bounds must catch
+    hl = np.full(S, nh, np.uint32)
+    hl[S // 2:] = rng.integers(0, nh + 1, S - S // 2)
+    for al, be, ga in ((0.2, 0.05, 0.3), (0.9, 0.5, 0.9)):
+        g, tb = params(ma_mode=A.FM_MODEL_HOLT_WINTERS, season_len=m, smooth_alpha=al, smooth_beta=be, smooth_gamma=ga,
+                       min_hist_points=1, pairwise_mode=A.FM_PW_NONE)
+        out, _, _ = both(ctx, g, tb, cur, None, hist, hist_len=hl, strategy=A.FM_STRAT_HISTORICAL,
+                         metric_type=rng.integers(0, 6, S).astype(np.uint8))
+        assert (out["rec"]["verdict"] == A.FM_UNHEALTHY).any()
+    if nh <= 2048:      # the baseline row as the model window of a canary batch, pairwise tests beside it
+        g, tb = params(ma_mode=A.FM_MODEL_HOLT_WINTERS, season_len=m, min_hist_points=1)
+        both(ctx, g, tb, cur, hist, metric_type=rng.integers(0, 6, S).astype(np.uint8))
+
+
+@pytest.mark.parametrize("nh,nc", [(3, 1), (10, 5), (100, 60), (1440, 60), (10080, 64), (333, 300)])
+def test_bivariate_pairs(ctx, nh, nc):
+    """fm_score_pairs (bivariate normal, docs/guides/design.md:67-76) against the oracle: moments
+    within 1e-6, flags exact; ragged lengths, correlated / independent / collinear / constant
+    histories, memory-like magnitudes."""
+    from test_oracle import pair_batch
+    rng = np.random.default_rng(nh * 131 + nc)
+    P = 64
+    z = rng.normal(0, 1, (P, nh + nc, 2))
+    rho = rng.uniform(-0.95, 0.95, (P, 1))
+    x = 1.0e3 + 25 * z[..., 0]
+    y = 7.0 + 2 * (rho * z[..., 0] + np.sqrt(1 - rho ** 2) * z[..., 1])
+    x[:8] = 1.0e9 + 6.4e4 * np.round(z[:8, :, 0] * 20)           # memory-like: sigma / mean ~ 1e-3, quantised
+    hx, hy = x[:, :nh].astype(np.float32), y[:, :nh].astype(np.float32)
+    cx, cy = x[:, nh:].astype(np.float32), y[:, nh:].astype(np.float32)
+    cx[::3, 0] += 200.0
+    hy[8] = 3.0 * hx[8]                                            # collinear
+    hx[9] = 5.0                                                    # constant
+    hl = np.full(P, nh, np.uint32); hl[32:] = rng.integers(0, nh + 1, P - 32)
+    cl = np.full(P, nc, np.uint32); cl[48:] = rng.integers(0, nc + 1, P - 48)
+    mt = rng.integers(0, 6, P).astype(np.uint8)
+    g, t = params(min_hist_points=3)
+    ctx.set_params(g, t)
+    out = ctx.score_pairs(cx, cy, hx, hy, cur_len=cl, hist_len=hl, metric_type=mt)
+    b, keep = pair_batch(cx, cy, hx, hy, cl, hl, mt)
+    ora = O.score_pairs(g, t, b)
+    got = out["rec"]
+    assert (got["status"] == ora["status"]).all()
+    scale = np.maximum(np.abs(ora["mean_x"]) + np.abs(ora["mean_y"]), 1.0)
+    for f in ("mean_x", "mean_y", "var_x", "var_y", "cov_xy"):
+        assert np.isclose(got[f], ora[f], rtol=1e-6, atol=1e-12 * scale * scale).all(), f
+    # knife edge: a pair whose distance is within 1e-6 of k^2 may flip; anything else is exact
+    k2 = np.array([t[int(m)].k ** 2 for m in mt])
+    edge = np.abs(ora["d2_max"] - k2) <= 1e-6 * k2
+    same = (got["n_anom"] == ora["n_anom"]) & (got["anom_mask"] == ora["anom_mask"]) & (got["verdict"] == ora["verdict"]) & \
+           (got["first_idx"] == ora["first_idx"])
+    assert (same | edge).all()
+    assert np.isclose(got["d2_max"], ora["d2_max"], rtol=1e-5, atol=1e-9).all()
+    if nh >= 100:
+        assert (got["verdict"] == A.FM_UNHEALTHY).any() and (got["verdict"] == A.FM_UNKNOWN).any()
+
+
 def test_rank_dump(ctx):
     rng = np.random.default_rng(2)
     for nc, nb in [(5, 9), (60, 1440), (64, 64), (1, 0), (0, 3)]:
