@@ -188,6 +188,8 @@ def canary_kernel_name(n_cur, n_base):
     """Which kernel plan_score (csrc/fm_api.cu) picks for a canary batch of this shape."""
     if n_cur <= 63 and n_base <= 2048:
         return "k_canary_count"
+    if n_cur <= 63 and n_base <= 16320:
+        return "k_canary_team"
     if n_cur <= 64 and n_base <= 2048:
         r = 16 if n_base <= 512 else 32 if n_base <= 1024 else 64
         return "k_canary_sort<%d, %d>" % (r, 3 * r // 4 if n_base <= 24 * r else r)

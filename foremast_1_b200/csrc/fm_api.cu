@@ -131,7 +131,7 @@ uint32_t round4(uint32_t n) { return (n + 3u) & ~3u; }
 bool mode_has(uint32_t mode, uint32_t t) { return mode == t || mode == FM_PW_ALL || mode == FM_PW_ANY; }
 
 // kind: 0 = k_score_series (generic), 2 = k_canary_sort<regs>, 3 = k_canary_elect<regs>, 4 = k_ma_only<regs>,
-// 5 = k_canary_count
+// 5 = k_canary_count, 6 = k_canary_team (baselines above 2048 points)
 struct Plan { FmKArgs a; int wpc; int grid; bool fast; int kind; int regs; int valid; };
 
 void fill_common(fm_ctx* c, const fm_batch* b, bool canary, FmKArgs& a) {
@@ -240,6 +240,18 @@ int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
   const size_t sm_total = 233472;
   if (!c->count_smem_set) { FM_CK(c, fm_canary_count_smem_attr((int)limit)); c->count_smem_set = 1; }
   fill_common(c, b, true, a);
+  if (b->n_base > 2048u) {
+    // long baselines: a team of 8 warps per series shares the stage and the table (k_canary_team);
+    // its last-resort direct count parks 2 x 256 words in the table area
+    if (slots < 512u) { slots = 512u; a.log_m = slots; }
+    a.warp_bytes = (uint32_t)((fm_canary_team_fixed_bytes() + (size_t)cap * 4 + (size_t)slots * 8 + 127) & ~size_t(127));
+    if (a.warp_bytes > limit) return fail(c, FM_E_UNSUPPORTED, "canary counting path does not fit shared memory");
+    const int ctas = std::max(1, std::min(2, (int)(sm_total / ((size_t)a.warp_bytes + 1024))));
+    pl->wpc = 8;
+    pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * ctas, b->n_series));
+    pl->fast = true; pl->kind = 6; pl->regs = nv; pl->valid = ns;
+    return FM_OK;
+  }
   a.warp_bytes = (uint32_t)((fm_canary_count_fixed_bytes() + (size_t)(64 + cap) * 4 + (size_t)slots * 8 + 127) & ~size_t(127));
   const int max_warps = c->count_warps ? c->count_warps : 16;     // 128 registers per thread
   int best_w = 1, best_total = 0;
@@ -293,7 +305,7 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
     return plan_ma_only(c, b, pl);
   if (canary && c->force_path != 1 && b->n_cur <= 64 && b->n_base >= 1 && !holt_winters) {
     if (c->force_path == 3 && b->n_base <= 2048) return plan_canary_elect(c, b, pl);
-    if (c->force_path != 2 && b->n_cur <= 63 && b->n_base <= 2048) return plan_canary_count(c, b, pl);
+    if (c->force_path != 2 && b->n_cur <= 63 && b->n_base <= 16320) return plan_canary_count(c, b, pl);
     if (b->n_base <= 2048) return plan_canary_sort(c, b, pl);
   }
   a.cur_cap = std::max(4u, round4(b->n_cur));
@@ -349,6 +361,7 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
 }
 
 int launch_plan(const Plan& pl, cudaStream_t st) {
+  if (pl.kind == 6) return fm_launch_canary_team(pl.a, pl.wpc, pl.grid, st);
   if (pl.kind == 5) return fm_launch_canary_count(pl.a, pl.wpc, pl.grid, st);
   if (pl.kind == 4) return fm_launch_ma_only(pl.a, pl.regs, pl.grid, st);
   if (pl.kind == 3) return fm_launch_canary_elect(pl.a, pl.regs, pl.grid, st);

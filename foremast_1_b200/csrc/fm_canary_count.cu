@@ -257,11 +257,22 @@ __device__ __forceinline__ void finish_stats(const FmKArgs& a, const fm_global_p
   }
   if (run_kw && lane == 2) {
     const long long Ni = (long long)nc + nb, r2y = Ni * (Ni + 1) - r2c;
-    const long long A = 3ll * (r2c * r2c * (long long)nb + r2y * r2y * (long long)nc) -
-                        3ll * (Ni + 1) * (Ni + 1) * Ni * (long long)nc * (long long)nb;
+    double dA;
+    if (Ni <= 4096) {                                                // every product below 2^63
+      const long long A = 3ll * (r2c * r2c * (long long)nb + r2y * r2y * (long long)nc) -
+                          3ll * (Ni + 1) * (Ni + 1) * Ni * (long long)nc * (long long)nb;
+      dA = (double)A;
+    } else {                                                         // long baselines: 128-bit integers
+      const __int128 A = (__int128)3 * ((__int128)(r2c * r2c) * nb + (__int128)r2y * r2y * nc) -
+                         (__int128)3 * (Ni + 1) * (Ni + 1) * Ni * ((__int128)nc * nb);
+      const bool neg = A < 0;
+      const unsigned __int128 M = neg ? (unsigned __int128)(-A) : (unsigned __int128)A;
+      dA = (double)(unsigned long long)(M >> 64) * 18446744073709551616.0 + (double)(unsigned long long)M;
+      if (neg) dA = -dA;
+    }
     num = 1.0;
     P = dn1 * dn2 * (N * N * N - N - dT);
-    Q = 0.5 * (double)A * (N - 1.0);                                 // Q / P = H / 2
+    Q = 0.5 * dA * (N - 1.0);                                        // Q / P = H / 2
   }
   if (fuse_model && model_ok) {
     if (lane == 3) {
@@ -624,6 +635,344 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
   }
 }
 
+// =================================================================================================
+// k_canary_team — the same algorithm with SEVERAL warps per series (one CTA per series), for
+// baselines above 2048 points (BASELINE.json configs[1] read literally: Mann-Whitney of 60 points
+// against the 10080-point window).  A 10080-point row needs 40 KB of stage and a 56 KB multiset
+// table: a warp on its own would own 100 KB and two warps would fill an SM.  A team of W = 8 warps
+// shares them: 16 warps per SM, every lane still handles ~40 keys, and U stays a search per key, so
+// the cost per key is that of the 1440-point kernel.
+//   warp 0    sorts the current row and builds the search tables, then turns the integers into the
+//             record (a5..a9);
+//   warp 1    runs the Wilcoxon test and the separate-history model;
+//   all       rank their share of the baseline's vector rows (warp w: rows [NV w / W, NV (w+1) / W));
+//             the last warp also takes the scalar rows and the current points.
+// CTA barriers: after pass A, around every overflow round, before the hand-over of the partial
+// sums.  Each warp's overflow lists grow into ITS part of the stage behind its own read position.
+//
+// Stage (floats): [current 64][pad 32][baseline cap][pad 64]; warp 0's lists start at word 0, warp
+// w's at the first word of its first vector row.
+constexpr uint32_t kPairCurPad = 96;     // floats before the baseline row
+constexpr uint32_t kPairTailPad = 64;    // floats behind it
+constexpr uint32_t kTeamMaxWarps = 16;
+constexpr uint32_t kXchgBytes = kTeamMaxWarps * 96;
+
+struct PairXchg {                         // warp w -> warp 0 (one entry per warp)
+  double s1, s2, mean, sigma;
+  unsigned long long t3, t_extra;
+  uint32_t sum_lu, np, wp2, wm2, twx, flags;   // flags: bit 0 Wilcoxon ran, bit 1 model ok
+};
+
+__device__ __forceinline__ void issue_rows_pair(const FmKArgs& a, float* stage, uint64_t* bar, uint64_t s,
+                                                uint32_t nc, uint32_t nb) {
+  const uint32_t cb = ((nc + 3u) & ~3u) * 4u, bb = ((nb + 3u) & ~3u) * 4u;
+  fm_mbar_expect_tx(bar, cb + bb);
+  if (cb) fm_bulk_g2s(stage, a.cur + s * a.cur_pitch, cb, bar);
+  if (bb) fm_bulk_g2s(stage + kPairCurPad, a.base + s * a.base_pitch, bb, bar);
+}
+
+__global__ void __launch_bounds__(512, 1) k_canary_team(const FmKArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const uint32_t NV = a.cnt_nv, NS = a.cnt_ns;
+  const uint32_t kCap = 128u * NV + 32u * NS;
+  const int lane = threadIdx.x & 31;
+  const uint32_t warp = threadIdx.x >> 5, W = blockDim.x >> 5;
+  const bool w0 = warp == 0, w1 = warp == 1, wlast = warp == W - 1u;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
+  float* stage = reinterpret_cast<float*>(smem + 16);
+  const uint32_t stage_s = fm_smem_u32(stage), base_s = stage_s + kPairCurPad * 4u;
+  const uint32_t search_s = stage_s + (kPairCurPad + a.base_cap + kPairTailPad) * 4u;
+  const uint32_t final_s = search_s + kSearchBytes;
+  PairXchg* xchg = reinterpret_cast<PairXchg*>(smem + 16 + (kPairCurPad + a.base_cap + kPairTailPad) * 4u +
+                                               kSearchBytes + kFinalBytes);
+  const uint32_t tbl_s = final_s + kFinalBytes + kXchgBytes;
+  const uint32_t m_slots = a.log_m, c_off = 4u * a.log_m;
+  const fm_global_params& g = a.P->g;
+  // my vector rows of the baseline; the last warp also takes the scalar rows and the current points
+  const uint32_t r0 = NV * warp / W, r1 = NV * (warp + 1u) / W;
+  const uint32_t list0 = (w0 ? stage_s : base_s + 512u * r0) + 4u * (uint32_t)lane;
+
+  if (threadIdx.x == 0) { fm_mbar_init(bar, 1); fm_fence_mbar_init(); }
+  __syncthreads();
+
+  uint64_t s = blockIdx.x;
+  uint32_t phase = 0;
+  if (s < a.n_series && threadIdx.x == 0)
+    issue_rows_pair(a, stage, bar, s, row_len(a.cur_len, s, a.n_cur), row_len(a.base_len, s, a.n_base));
+
+  for (; s < a.n_series; s += gridDim.x) {
+    const uint32_t nc = row_len(a.cur_len, s, a.n_cur);
+    const uint32_t nb = row_len(a.base_len, s, a.n_base);
+    const uint64_t sn = s + gridDim.x;
+    if (sn < a.n_series) {     // pull the next rows into L2 while this series is ranked
+      const uint32_t nbn = row_len(a.base_len, sn, a.n_base);
+      const char* pb = reinterpret_cast<const char*>(a.base + sn * a.base_pitch);
+      for (uint32_t o = threadIdx.x * 128u; o < nbn * 4u; o += blockDim.x * 128u) fm_prefetch_l2(pb + o);
+      if (threadIdx.x < 2) fm_prefetch_l2(reinterpret_cast<const char*>(a.cur + sn * a.cur_pitch) + threadIdx.x * 128);
+    }
+    fm_mbar_wait(bar, phase);
+    phase ^= 1u;
+
+    const bool pair = g.pairwise_mode != FM_PW_NONE && nc > 0 && nb > 0;
+    const bool want_mw = pair && fm_mode_has(g.pairwise_mode, FM_PW_MANN_WHITE) && nc >= g.min_mw && nb >= g.min_mw;
+    const bool want_kw = pair && fm_mode_has(g.pairwise_mode, FM_PW_KRUSKAL) && nc >= g.min_kw && nb >= g.min_kw;
+    const bool want_wx = pair && fm_mode_has(g.pairwise_mode, FM_PW_WILCOXON);
+    const bool ranks = want_mw || want_kw;
+    const bool fuse_model = (a.hist == nullptr) && g.ma_mode == FM_MA_ALL;
+
+    const bool va = (uint32_t)lane < nc, vb = (uint32_t)lane + 32u < nc;
+    const float craw_a = va ? fm_lds_f32(stage_s + 4u * lane) : 0.0f;
+    const float craw_b = vb ? fm_lds_f32(stage_s + 4u * (lane + 32u)) : 0.0f;
+    const float ca = va ? craw_a + 0.0f : CUDART_INF_F;
+    const float cb = vb ? craw_b + 0.0f : CUDART_INF_F;
+    const uint32_t hka = va ? __float_as_uint(ca) : kNoKey, hkb = vb ? __float_as_uint(cb) : kNoKey;
+    const uint32_t mult0 = mult_of(0);
+    const float nokey = __uint_as_float(kNoKey);
+
+    // ---- role phase: warp 0 sorts the current row, warp 1 runs Wilcoxon and the separate models ----
+    WxInts wx = {0u, 0u, 0u, 0u, false};
+    ModelOut mo = {0.0, 0.0, false};
+    if (w0) {
+      if (ranks) {
+        float sa = ca, sb = cb;
+        sort64(sa, sb, lane);
+        const float qa = __shfl_up_sync(FM_FULL, sa, 1);
+        const float last_a = __shfl_sync(FM_FULL, sa, 31);
+        float qb = __shfl_up_sync(FM_FULL, sb, 1);
+        if (lane == 0) qb = last_a;
+        const uint32_t ba = __ballot_sync(FM_FULL, lane == 0 || qa != sa), bb = __ballot_sync(FM_FULL, qb != sb);
+        uint32_t lo_a, e_a, lo_b, e_b;
+        runs_from_ballots(ba, bb, lane, lo_a, e_a, lo_b, e_b);
+        const uint32_t rl_a = min(e_a, nc) - min(lo_a, nc), rl_b = min(e_b, nc) - min(lo_b, nc);
+        fm_sts_f32(search_s + 4u * lane, sa);
+        fm_sts_f32(search_s + 4u * (lane + 33u), sb);
+        sts_v2(final_s + 8u * lane, __float_as_uint(sa), (rl_a << 16) | (2u * lane));
+        sts_v2(final_s + 8u * (lane + 33u), __float_as_uint(sb), (rl_b << 16) | (2u * (lane + 32u)));
+      }
+    } else if (w1) {
+      if (want_wx) wx = wilcoxon_ints(g, wilcoxon_load(g, stage_s, nc, nb, lane, kPairCurPad), lane);
+      if (a.hist) mo = model_call(&g, a.hist + s * a.hist_pitch, row_len(a.hist_len, s, a.n_hist), true, lane);
+      else if (!fuse_model) mo = model_call(&g, stage + kPairCurPad, nb, false, lane);
+    }
+
+    // ---- sweep 1 over my rows: moments, election pass A --------------------------------------------
+    const double pivot = nb ? (double)fm_lds_f32(base_s) : 0.0;
+    FmMom mom = {0.0, 0.0};
+    const uint32_t nfull = min(r1, max(r0, nb >> 7));        // my rows in [r0, nfull) have no missing point
+    if (ranks) {
+      for (uint32_t o = threadIdx.x * 16u; o < c_off; o += blockDim.x * 16u) sts_zero16(tbl_s + c_off + o);
+      if (wlast) {
+        fm_sts_u32(tbl_s + slot_of(hka, mult0, m_slots), hka);
+        fm_sts_u32(tbl_s + slot_of(hkb, mult0, m_slots), hkb);
+      }
+    }
+    if (ranks || fuse_model) {
+#pragma unroll 1
+      for (uint32_t c = r0; c < nfull; ++c) {
+        const float4 q = fm_lds_v4(base_s + (((uint32_t)lane + 32u * c) << 4));
+        if (fuse_model) {
+          fm_mom_add(mom, q.x, pivot); fm_mom_add(mom, q.y, pivot);
+          fm_mom_add(mom, q.z, pivot); fm_mom_add(mom, q.w, pivot);
+        }
+        if (ranks) {
+          const uint32_t k0 = __float_as_uint(q.x + 0.0f), k1 = __float_as_uint(q.y + 0.0f),
+                         k2 = __float_as_uint(q.z + 0.0f), k3 = __float_as_uint(q.w + 0.0f);
+          fm_sts_u32(tbl_s + slot_of(k0, mult0, m_slots), k0);
+          fm_sts_u32(tbl_s + slot_of(k1, mult0, m_slots), k1);
+          fm_sts_u32(tbl_s + slot_of(k2, mult0, m_slots), k2);
+          fm_sts_u32(tbl_s + slot_of(k3, mult0, m_slots), k3);
+        }
+      }
+#pragma unroll 1
+      for (uint32_t c = nfull; c < r1; ++c) {
+        float k[4];
+        float4 q;
+        const uint32_t e0 = keys4(base_s, c, lane, nb, nokey, k, q);
+        if (fuse_model) {
+          if (e0 < nb) fm_mom_add(mom, q.x, pivot);
+          if (e0 + 1u < nb) fm_mom_add(mom, q.y, pivot);
+          if (e0 + 2u < nb) fm_mom_add(mom, q.z, pivot);
+          if (e0 + 3u < nb) fm_mom_add(mom, q.w, pivot);
+        }
+        if (ranks) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) fm_sts_u32(tbl_s + slot_of(__float_as_uint(k[i]), mult0, m_slots), __float_as_uint(k[i]));
+        }
+      }
+      if (wlast) {
+#pragma unroll 1
+        for (uint32_t j = 0; j < NS; ++j) {
+          const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
+          float v = nokey;
+          if (e < nb) {
+            const float q = fm_lds_f32(base_s + (e << 2));
+            v = q + 0.0f;
+            if (fuse_model) fm_mom_add(mom, q, pivot);
+          }
+          if (ranks) fm_sts_u32(tbl_s + slot_of(__float_as_uint(v), mult0, m_slots), __float_as_uint(v));
+        }
+      }
+    }
+    __syncthreads();                                         // pass A, counters and search tables complete
+
+    // ---- sweep 2 over my rows, overflow rounds ----------------------------------------------------------
+    Tie tie = {0u, 0u};
+    unsigned long long tsq = 0, tlin = 0;              // long rows: p^2 sums leave 32 bits, so flush per group
+    auto flush = [&]() { tsq += tie.sq; tlin += 0u - tie.lin; tie.sq = 0u; tie.lin = 0u; };
+    uint32_t acc_all = 0, acc_eq = 0;
+    unsigned long long t_extra = 0;
+    if (ranks) {
+      const float c31 = fm_lds_f32(search_s + 124u);
+      const uint32_t final_k = final_s - 2u * search_s;
+      uint32_t lptr = list0;
+      uint32_t c = r0;
+#pragma unroll 1
+      for (; c + 2u <= nfull; c += 2u) {
+        const float4 q0 = fm_lds_v4(base_s + (((uint32_t)lane + 32u * c) << 4));
+        const float4 q1 = fm_lds_v4(base_s + (((uint32_t)lane + 32u * c + 32u) << 4));
+        const float k[8] = {q0.x + 0.0f, q0.y + 0.0f, q0.z + 0.0f, q0.w + 0.0f,
+                            q1.x + 0.0f, q1.y + 0.0f, q1.z + 0.0f, q1.w + 0.0f};
+        rank_group<8>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
+        flush();
+      }
+#pragma unroll 1
+      for (; c < r1; ++c) {
+        float k[4];
+        float4 q;
+        keys4(base_s, c, lane, nb, nokey, k, q);
+        rank_group<4>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
+        flush();
+      }
+      if (wlast) {
+#pragma unroll 1
+        for (uint32_t j = 0; j < NS; ++j) {
+          const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
+          const float k = e < nb ? fm_lds_f32(base_s + (e << 2)) + 0.0f : nokey;
+          rank_group<1>(&k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
+          flush();
+        }
+        const uint32_t ck[2] = {hka, hkb};                     // the current points last: their list rows are the tail pad
+        classify<2>(ck, tbl_s, c_off, mult0, m_slots, tie, lptr);
+        flush();
+      }
+
+      uint32_t n_l = (lptr - list0) >> 7;
+      for (uint32_t round = 1;; ++round) {
+        if (!__syncthreads_or(n_l > 0u)) break;                // also: everybody's previous pass B is complete
+        if (round == kMaxRounds) {
+          // Not reached in practice.  What is left are whole classes: count each key's class directly.
+          // (the tables are dead by now: their first words take every thread's list length and base)
+          fm_sts_u32(tbl_s + 4u * threadIdx.x, n_l);
+          fm_sts_u32(tbl_s + 2048u + 4u * threadIdx.x, list0);
+          __syncthreads();
+          for (uint32_t k = 0; k < n_l; ++k) {
+            const uint32_t mine = fm_lds_u32(list0 + 128u * k);
+            uint32_t t = 0;
+            for (uint32_t l2 = 0; l2 < blockDim.x; ++l2) {
+              const uint32_t n2 = fm_lds_u32(tbl_s + 4u * l2), b2 = fm_lds_u32(tbl_s + 2048u + 4u * l2);
+              for (uint32_t k2 = 0; k2 < n2; ++k2) t += fm_lds_u32(b2 + 128u * k2) == mine;
+            }
+            t_extra += (unsigned long long)t * t - 1ull;
+          }
+          break;
+        }
+        for (uint32_t o = threadIdx.x * 16u; o < c_off; o += blockDim.x * 16u) sts_zero16(tbl_s + c_off + o);
+        const uint32_t mult = mult_of(round);
+        {
+          uint32_t k = 0;
+          for (; k + 4u <= n_l; k += 4u) {
+            uint32_t bits[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) bits[i] = fm_lds_u32(list0 + 128u * (k + i));
+#pragma unroll
+            for (int i = 0; i < 4; ++i) fm_sts_u32(tbl_s + slot_of(bits[i], mult, m_slots), bits[i]);
+          }
+          for (; k < n_l; ++k) {
+            const uint32_t bits = fm_lds_u32(list0 + 128u * k);
+            fm_sts_u32(tbl_s + slot_of(bits, mult, m_slots), bits);
+          }
+        }
+        __syncthreads();
+        uint32_t wptr = list0;
+        {
+          uint32_t k = 0;
+          for (; k + 4u <= n_l; k += 4u) {
+            uint32_t bits[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) bits[i] = fm_lds_u32(list0 + 128u * (k + i));
+            classify<4>(bits, tbl_s, c_off, mult, m_slots, tie, wptr);
+            flush();
+          }
+          for (; k < n_l; ++k) {
+            const uint32_t bits = fm_lds_u32(list0 + 128u * k);
+            classify<1>(&bits, tbl_s, c_off, mult, m_slots, tie, wptr);
+            flush();
+          }
+        }
+        n_l = (wptr - list0) >> 7;
+      }
+    }
+
+    // ---- partial sums; warp 1 hands its own over -------------------------------------------------------
+    uint32_t sum_lu = 0;
+    unsigned long long t3 = 0, tx = 0;
+    if (ranks) {
+      sum_lu = __reduce_add_sync(FM_FULL, (acc_all & 0xFFFFu) + (acc_eq >> 16));
+      t3 = (unsigned long long)fm_warp_sum((long long)(tsq + tlin));
+      tx = (unsigned long long)fm_warp_sum((long long)t_extra);
+    }
+    double s1 = 0.0, s2 = 0.0;
+    if (fuse_model) { s1 = fm_warp_sum(mom.s1); s2 = fm_warp_sum(mom.s2); }
+    if (!w0 && lane == 0) {
+      PairXchg& x = xchg[warp];
+      x.s1 = s1; x.s2 = s2; x.mean = mo.mean; x.sigma = mo.sigma;
+      x.t3 = t3; x.t_extra = tx; x.sum_lu = sum_lu;
+      x.np = wx.np; x.wp2 = wx.wp2; x.wm2 = wx.wm2; x.twx = wx.t;
+      x.flags = (wx.run ? 1u : 0u) | (mo.ok ? 2u : 0u);
+    }
+    __syncthreads();                                         // hand-over visible; nobody reads the stage any more
+    if (sn < a.n_series && threadIdx.x == 0) {
+      fm_fence_proxy_async();
+      issue_rows_pair(a, stage, bar, sn, row_len(a.cur_len, sn, a.n_cur), row_len(a.base_len, sn, a.n_base));
+    }
+    if (!w0) continue;                                       // the others go on to the next series
+
+    // ---- warp 0: a5..a9 -----------------------------------------------------------------------------------
+    PairXchg x1 = xchg[1];                                   // warp 1: Wilcoxon and the model; all: partial sums
+    for (uint32_t w = 2; w < W; ++w) {
+      x1.s1 += xchg[w].s1; x1.s2 += xchg[w].s2; x1.t3 += xchg[w].t3; x1.t_extra += xchg[w].t_extra;
+      x1.sum_lu += xchg[w].sum_lu;
+    }
+    const uint32_t ty = a.metric_type ? a.metric_type[s] : 0u;
+    const fm_type_params tp = a.P->types[ty < a.P->n_types ? ty : 0u];
+    fm_series_rec rec;
+    fm_rec_init(rec);
+    fm_rank_aux ax = {0, 0, 0, 0, 0, 0u, 0u};
+    uint32_t status = 0;
+    if (nc == 0) status |= FM_ST_NO_CURRENT;
+    wx.np = x1.np; wx.wp2 = x1.wp2; wx.wm2 = x1.wm2; wx.t = x1.twx; wx.run = (x1.flags & 1u) != 0;
+    ax.n_wx = wx.np;
+    bool model_ok;
+    if (fuse_model) {
+      model_ok = nb >= max(g.min_hist_points, g.ddof + 1u);
+      s1 += x1.s1; s2 += x1.s2;
+    } else {
+      model_ok = (x1.flags & 2u) != 0;
+      rec.mean = x1.mean; rec.sigma = x1.sigma;
+    }
+    if (!model_ok) status |= FM_ST_HIST_INSUFFICIENT;
+    long long r2c = 0, Tt = 0;
+    if (ranks) {
+      r2c = (long long)nc * (nc + 1) + 2ll * nc * nb - (long long)(sum_lu + x1.sum_lu);
+      const unsigned long long ninv = (unsigned long long)(kCap - nb) + (64u - nc);
+      Tt = (long long)(3ull * (t3 + x1.t3) + tx + x1.t_extra - (ninv * ninv * ninv - ninv));
+      ax.r2_cur = r2c; ax.t_mw = Tt;
+    }
+    finish_stats(a, g, tp, s, lane, nc, nb, pair, want_mw, want_kw, wx, fuse_model, model_ok, s1, s2, pivot, r2c, Tt,
+                 craw_a, craw_b, va, vb, rec, ax, status);
+  }
+}
+
 }  // namespace
 
 // tiers (vector rows, scalar rows) -> capacity 128 NV + 32 NS baseline points.  The rows are walked
@@ -632,14 +981,22 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
 #define FM_COUNT_TIERS(X) X(1, 0) X(2, 0) X(4, 0) X(8, 0) X(11, 1) X(12, 0) X(16, 0)
 
 cudaError_t fm_canary_count_smem_attr(int bytes) {
-  return cudaFuncSetAttribute(k_canary_count, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  cudaError_t e = cudaFuncSetAttribute(k_canary_count, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_canary_team, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  return e;
 }
 
-// smallest tier that holds n_base points; 0 if none does
+// smallest tier that holds n_base points; 0 if none does.  Above 2048 points (k_canary_team) the
+// tier is the row itself: whole vector rows plus the scalar rows of the remainder.
 uint32_t fm_canary_count_tier(uint32_t n_base, int* nv, int* ns) {
 #define X(NV, NS) if (n_base <= 128u * NV + 32u * NS) { *nv = NV; *ns = NS; return 128u * NV + 32u * NS; }
   FM_COUNT_TIERS(X)
 #undef X
+  if (n_base <= 16320u) {
+    *nv = (int)(n_base / 128u);
+    *ns = (int)((n_base % 128u + 31u) / 32u);
+    return 128u * (uint32_t)*nv + 32u * (uint32_t)*ns;
+  }
   return 0;
 }
 
@@ -647,5 +1004,16 @@ size_t fm_canary_count_fixed_bytes() { return 16 + kSearchBytes + kFinalBytes; }
 int fm_launch_canary_count(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st) {
   const size_t smem = (size_t)warps_per_cta * a.warp_bytes;
   k_canary_count<<<grid, warps_per_cta * 32, smem, st>>>(a);
+  return 1;
+}
+
+// k_canary_team: bytes per CTA beside the baseline capacity and the multiset table
+size_t fm_canary_team_fixed_bytes() {
+  return 16 + (size_t)(kPairCurPad + kPairTailPad) * 4 + kSearchBytes + kFinalBytes + kXchgBytes;
+}
+
+// a.warp_bytes = bytes of shared memory per CTA (= per series in flight)
+int fm_launch_canary_team(const FmKArgs& a, int warps, int grid, cudaStream_t st) {
+  k_canary_team<<<grid, warps * 32, a.warp_bytes, st>>>(a);
   return 1;
 }

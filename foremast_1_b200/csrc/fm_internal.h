@@ -68,6 +68,8 @@ int fm_launch_canary_elect(const FmKArgs& a, int nv, int grid, cudaStream_t st);
 int fm_launch_canary_count(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st);
 uint32_t fm_canary_count_tier(uint32_t n_base, int* nv, int* ns);
 size_t fm_canary_count_fixed_bytes();
+size_t fm_canary_team_fixed_bytes();
+int fm_launch_canary_team(const FmKArgs& a, int warps, int grid, cudaStream_t st);
 cudaError_t fm_canary_count_smem_attr(int bytes);
 size_t fm_canary_elect_fixed_bytes();
 int fm_launch_ma_only(const FmKArgs& a, int group, int grid, cudaStream_t st);

@@ -182,6 +182,27 @@ def test_sort_kernel_tiers(ctx, nb):
     both(ctx, g, t, cur, base, base_len=bl, metric_type=rng.integers(0, 6, S).astype(np.uint8))
 
 
+@pytest.mark.parametrize("nb", [2049, 2176, 4095, 4096, 8000, 10080, 16320])
+def test_long_baselines(ctx, nb):
+    """Baselines above 2048 points (BASELINE configs[1] read literally: 60 points against the 7-day
+    window) go to the team form of the counting kernel: both sides of its row boundaries, heavy ties
+    (runs of thousands of keys, p^2 sums beyond 32 bits), ragged lengths down to one point."""
+    rng = np.random.default_rng(nb)
+    S = 40
+    cur = rng.normal(100, 3, (S, 60)).astype(np.float32)
+    base = rng.normal(100, 3, (S, nb)).astype(np.float32)
+    base[:10] = np.round(base[:10])
+    cur[:10] = np.round(cur[:10])
+    base[10:14] = 7.0                                       # one class of nb keys
+    cur[10:12] = 7.0
+    base[14:18, : nb // 2] = base[14:18, :1]
+    bl = np.full(S, nb, np.uint32)
+    bl[24:] = rng.integers(1, nb + 1, S - 24)
+    bl[24:28] = [1, 20, 2049, nb - 1]
+    g, t = params(min_hist_points=1)
+    both(ctx, g, t, cur, base, base_len=bl, metric_type=rng.integers(0, 6, S).astype(np.uint8))
+
+
 def test_param_variants(ctx):
     d = synth_desc(3, 800, 60, 1440, 0)
     cur, base, _, mt = synth_host(d)
