@@ -138,7 +138,7 @@ void fill_common(fm_ctx* c, const fm_batch* b, bool canary, FmKArgs& a) {
   a.cur = b->cur; a.cur_len = b->cur_len; a.n_cur = b->n_cur; a.cur_pitch = b->cur_pitch;
   a.base = canary ? b->base : nullptr; a.base_len = b->base_len; a.n_base = canary ? b->n_base : 0; a.base_pitch = b->base_pitch;
   a.hist = b->hist; a.hist_len = b->hist_len; a.n_hist = b->n_hist; a.hist_pitch = b->hist_pitch;
-  a.metric_type = b->metric_type; a.api_id = b->api_id;
+  a.metric_type = b->metric_type; a.api_id = b->api_id; a.n_apis = b->n_apis;
   a.n_series = b->n_series;
   a.P = c->d_params;
   a.record_kind = b->record_kind;
@@ -346,7 +346,7 @@ int32_t plan_score(fm_ctx* c, const fm_batch* b, Plan* pl) {
   a.cur = b->cur; a.cur_len = b->cur_len; a.n_cur = b->n_cur; a.cur_pitch = b->cur_pitch;
   a.base = canary ? b->base : nullptr; a.base_len = b->base_len; a.n_base = canary ? b->n_base : 0; a.base_pitch = b->base_pitch;
   a.hist = b->hist; a.hist_len = b->hist_len; a.n_hist = b->n_hist; a.hist_pitch = b->hist_pitch;
-  a.metric_type = b->metric_type; a.api_id = b->api_id;
+  a.metric_type = b->metric_type; a.api_id = b->api_id; a.n_apis = b->n_apis;
   a.n_series = b->n_series;
   a.P = c->d_params;
   a.record_kind = b->record_kind;
@@ -458,7 +458,7 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
     cudaError_t e__ = (call);                                                                  \
     if (e__ != cudaSuccess) {                                                                  \
       fail(nullptr, FM_E_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__));               \
-      delete c;                                                                                \
+      fm_ctx_destroy(c);   /* streams and events created so far go with it */                  \
       return FM_E_CUDA;                                                                        \
     }                                                                                          \
   } while (0)
@@ -989,8 +989,10 @@ static int32_t plan_groups(fm_ctx* c, const fm_group_batch* b, FmGArgs* a, int* 
   if (!b->group_offsets || (!b->cur && b->n_groups)) return fail(c, FM_E_INVALID, "null group_offsets / cur");
   if ((uint64_t)b->n_cur * FM_MAX_GROUPS > FM_MAX_RANK_N) return fail(c, FM_E_UNSUPPORTED, "n_cur %u too long for %u groups", b->n_cur, FM_MAX_GROUPS);
   if (c->params.g.ma_mode == FM_MODEL_HOLT_WINTERS) return fail(c, FM_E_UNSUPPORTED, "FM_MODEL_HOLT_WINTERS is a series-batch model (no pod-group form)");
-  if ((b->cur_pitch & 3u) || (b->hist && (b->hist_pitch & 3u)) || (reinterpret_cast<uintptr_t>(b->hist) & 15u))
-    return fail(c, FM_E_INVALID, "rows must be 16-byte aligned with pitch a multiple of 4");
+  if ((b->cur_pitch & 3u) || (b->hist && (b->hist_pitch & 3u)) || (reinterpret_cast<uintptr_t>(b->hist) & 15u) ||
+      (reinterpret_cast<uintptr_t>(b->cur) & 15u) || b->cur_pitch < ((b->n_cur + 3u) & ~3u) ||
+      (b->hist && b->hist_pitch < ((b->n_hist + 3u) & ~3u)))
+    return fail(c, FM_E_INVALID, "rows must be 16-byte aligned with pitch a multiple of 4 and >= roundup4(n)");
   a->raw_cap = std::max(64u, b->n_cur * FM_MAX_GROUPS);
   a->pool_cap = pow2_ceil(a->raw_cap, 64u);
   a->warp_bytes = (uint32_t)((((size_t)a->raw_cap + a->pool_cap) * 4 + 127) & ~size_t(127));
@@ -1060,6 +1062,13 @@ int32_t fm_score_groups(fm_ctx* c, const fm_group_batch* b, fm_series_rec* out, 
   FM_CK(c, cudaSetDevice(c->device));
   auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
   const uint64_t V = b->n_services, G = b->n_groups;
+  // the kernels index the output by these offsets: they must walk [0, n_groups] without a step back
+  if (!b->group_offsets) return fail(c, FM_E_INVALID, "null group_offsets");
+  if (b->group_offsets[0] != 0u || b->group_offsets[V] != G) return fail(c, FM_E_INVALID, "group_offsets must start at 0 and end at n_groups");
+  for (uint64_t v = 0; v < V; ++v) {
+    if (b->group_offsets[v + 1] < b->group_offsets[v]) return fail(c, FM_E_INVALID, "group_offsets must be non-decreasing (service %llu)", (unsigned long long)v);
+    if (b->group_offsets[v + 1] - b->group_offsets[v] > FM_MAX_GROUPS) return fail(c, FM_E_UNSUPPORTED, "service %llu has more than %u groups", (unsigned long long)v, FM_MAX_GROUPS);
+  }
   size_t o = 0;
   const size_t o_off = o;  o += al((V + 1) * 4);
   const size_t o_cur = o;  o += al(G * b->cur_pitch * 4);

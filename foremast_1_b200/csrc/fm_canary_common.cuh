@@ -259,7 +259,7 @@ __device__ __forceinline__ void finish_series(const FmKArgs& a, const fm_global_
   if (lane == 0) {
     fm_write_record(a.out, s, a.record_kind, rec);
     if (a.aux) a.aux[s] = ax;
-    if (a.api && a.api_id) fm_rollup_add(a.api, a.api_id[s], rec.verdict);
+    if (a.api && a.api_id) fm_rollup_add(a.api, a.api_id[s], a.n_apis, rec.verdict);
   }
 }
 

@@ -640,7 +640,8 @@ __device__ __forceinline__ void fm_write_record(void* out, uint64_t s, uint32_t 
 }
 
 // Fused roll-up (a9): the per-API counters live in the output records.
-__device__ __forceinline__ void fm_rollup_add(fm_rollup_rec* api, uint32_t id, uint32_t verdict) {
+__device__ __forceinline__ void fm_rollup_add(fm_rollup_rec* api, uint32_t id, uint32_t limit, uint32_t verdict) {
+  if (id >= limit) return;          // an id outside the caller's table is dropped, never written
   atomicAdd(&api[id].n_children, 1u);
   if (verdict == FM_UNHEALTHY) atomicAdd(&api[id].n_unhealthy, 1u);
   if (verdict == FM_UNKNOWN) atomicAdd(&api[id].n_unknown, 1u);

@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
       rec.status = (uint8_t)status;
       if (lane == 0) {
         a.out[g0 + k] = rec;
-        if (a.svc) fm_rollup_add(a.svc, (uint32_t)v, rec.verdict);
+        if (a.svc) fm_rollup_add(a.svc, (uint32_t)v, 0xFFFFFFFFu, rec.verdict);
       }
     }
     __syncwarp();

@@ -20,6 +20,7 @@ struct FmKArgs {
   const float* hist; const uint32_t* hist_len; uint32_t n_hist, hist_pitch;
   const uint8_t* metric_type;
   const uint32_t* api_id;
+  uint32_t n_apis;         // roll-up ids >= n_apis are dropped on the device
   uint64_t n_series;
   void* out;               // fm_series_rec[] or fm_compact_rec[]
   fm_rank_aux* aux;        // optional

@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(512) k_score_series(const FmKArgs a) {
     if (lane == 0) {
       fm_write_record(a.out, s, a.record_kind, rec);
       if (a.aux) a.aux[s] = ax;
-      if (a.api && a.api_id) fm_rollup_add(a.api, a.api_id[s], rec.verdict);
+      if (a.api && a.api_id) fm_rollup_add(a.api, a.api_id[s], a.n_apis, rec.verdict);
     }
     __syncwarp();
 
@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(512) k_score_groups(const FmGArgs a) {
       rec.status = (uint8_t)status;
       if (lane == 0) {
         a.out[g0 + k] = rec;
-        if (a.svc) fm_rollup_add(a.svc, (uint32_t)v, rec.verdict);
+        if (a.svc) fm_rollup_add(a.svc, (uint32_t)v, 0xFFFFFFFFu, rec.verdict);
       }
     }
     __syncwarp();
@@ -372,14 +372,14 @@ __global__ void __launch_bounds__(512) k_score_groups(const FmGArgs a) {
 // ---------------------------------------------------------------------------
 // a9: severity from the accumulated child counters, then service level.
 __global__ void k_rollup_severity(fm_rollup_rec* r, uint64_t n, const uint32_t* parent,
-                                  fm_rollup_rec* up) {
+                                  fm_rollup_rec* up, uint32_t n_up) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   fm_rollup_rec x = r[i];
   const uint32_t sev = x.n_unhealthy > 0 ? FM_UNHEALTHY
                      : (x.n_children > 0 && x.n_unknown == x.n_children) ? FM_UNKNOWN : FM_HEALTHY;
   r[i].severity = (uint8_t)sev;
-  if (up && parent) fm_rollup_add(up, parent[i], sev);
+  if (up && parent) fm_rollup_add(up, parent[i], n_up, sev);
 }
 
 // ---------------------------------------------------------------------------
@@ -487,11 +487,11 @@ int fm_launch_rollup_finalize(fm_rollup_rec* api, uint32_t n_apis, const uint32_
                               fm_rollup_rec* svc, uint32_t n_services, cudaStream_t st) {
   int n = 0;
   if (api && n_apis) {
-    k_rollup_severity<<<(n_apis + 255) / 256, 256, 0, st>>>(api, n_apis, svc ? api_service : nullptr, svc);
+    k_rollup_severity<<<(n_apis + 255) / 256, 256, 0, st>>>(api, n_apis, svc ? api_service : nullptr, svc, n_services);
     ++n;
   }
   if (svc && n_services) {
-    k_rollup_severity<<<(n_services + 255) / 256, 256, 0, st>>>(svc, n_services, nullptr, nullptr);
+    k_rollup_severity<<<(n_services + 255) / 256, 256, 0, st>>>(svc, n_services, nullptr, nullptr, 0u);
     ++n;
   }
   return n;
@@ -507,7 +507,7 @@ int fm_launch_gather_rows(const float* cache, uint32_t pitch, const uint32_t* d_
 
 int fm_launch_rollup_finalize_one(fm_rollup_rec* recs, uint64_t n, cudaStream_t st) {
   if (!recs || !n) return 0;
-  k_rollup_severity<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(recs, n, nullptr, nullptr);
+  k_rollup_severity<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(recs, n, nullptr, nullptr, 0u);
   return 1;
 }
 

@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs
         reinterpret_cast<fm_series_rec*>(a.out)[s] = r;
       }
       if (a.aux) a.aux[s] = fm_rank_aux{0, 0, 0, 0, 0, 0u, 0u};
-      if (a.api && a.api_id) fm_rollup_add(a.api, a.api_id[s], verdict);
+      if (a.api && a.api_id) fm_rollup_add(a.api, a.api_id[s], a.n_apis, verdict);
     }
   }
 }
