@@ -335,12 +335,23 @@ def _failed(reason):
             "gauges": []}
 
 
-def fetch_documents(docs, fetch=http_fetch):
+def row_id(doc_id, alias):
+    """64-bit id of one metric of one job for the device-resident row cache (FNV-1a)."""
+    h = 0xCBF29CE484222325
+    for b in f"{doc_id}|{alias}".encode("utf-8"):
+        h = ((h ^ b) * 0x100000001B3) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def fetch_documents(docs, fetch=http_fetch, resident=None):
     """Preprocessing (the state diagram's preprocess_* half): parse the three config strings of every
     document, fetch and decode the series.  Returns (series, failed): series = list of
     (doc index, alias, ts_cur, cur, base, hist); failed = {doc id: result} for documents whose configs
-    cannot be parsed or fetched ("preprocess_failed" with the reason; the others go on)."""
+    cannot be parsed or fetched ("preprocess_failed" with the reason; the others go on).
+    resident(ids) -> bool array (engine.Context.cache_query): the baseline / history of a metric
+    whose rows are still in HBM from the last poll are not fetched again (empty placeholders)."""
     series, failed = [], {}
+    empty = np.zeros(0, np.float32)
     for di, doc in enumerate(docs):
         try:
             cur_cfg = parse_config(doc.get("currentConfig", ""))
@@ -351,10 +362,14 @@ def fetch_documents(docs, fetch=http_fetch):
             # Document says historicalConfig, DocumentResponse historicConfig (models.go:92,130)
             hist_cfg = parse_config(doc.get("historicalConfig") or doc.get("historicConfig") or "")
             mine = []
-            for alias, url in cur_cfg.items():
+            here = None
+            if resident is not None:
+                here = resident(np.array([row_id(doc["id"], a) for a in cur_cfg], np.uint64))
+            for k, (alias, url) in enumerate(cur_cfg.items()):
                 ts, cur = merge_series(decode_response(fetch(url)))
-                base = merge_series(decode_response(fetch(base_cfg[alias])))[1] if alias in base_cfg else None
-                hist = merge_series(decode_response(fetch(hist_cfg[alias])))[1] if alias in hist_cfg else None
+                skip = here is not None and bool(here[k])
+                base = (empty if skip else merge_series(decode_response(fetch(base_cfg[alias])))[1]) if alias in base_cfg else None
+                hist = (empty if skip else merge_series(decode_response(fetch(hist_cfg[alias])))[1]) if alias in hist_cfg else None
                 mine.append((di, alias, ts, cur, base, hist))
             series += mine
         except Exception as e:  # host I/O problem: the document fails, the batch goes on
@@ -362,9 +377,11 @@ def fetch_documents(docs, fetch=http_fetch):
     return series, failed
 
 
-def score_series(ctx, docs, series, failed=None, type_names=None, max_hist=10080, max_base=None):
+def score_series(ctx, docs, series, failed=None, type_names=None, max_hist=10080, max_base=None, cached=False):
     """Postprocessing: every fetched metric of every document in ONE coalesced batch per strategy
-    kind, then per document the A.9 roll-up over its metrics, reason and anomalyInfo."""
+    kind, then per document the A.9 roll-up over its metrics, reason and anomalyInfo.
+    cached: score through the row cache (fm_score_batch_cached) — rows are then packed to the fixed
+    widths max_base / max_hist so that the resident layout never changes between polls."""
     type_names = type_names or dict(A.METRIC_TYPES)
     results = dict(failed or {})
     out = {}
@@ -381,15 +398,22 @@ def score_series(ctx, docs, series, failed=None, type_names=None, max_hist=10080
         hist = hl = base = bl = None
         if any(series[i][5] is not None for i in idx):
             hw = min(max_hist, max(1, max((series[i][5].size if series[i][5] is not None else 0) for i in idx)))
+            if cached:
+                hw = max_hist
             hist, hl = _rows(ctx, tag + "hist",
                              [series[i][5] if series[i][5] is not None else np.zeros(0, np.float32) for i in idx], hw)
         if canary:
             bw = max(1, max(series[i][4].size for i in idx))
             bw = min(bw, max_base or (A.FM_MAX_RANK_N - cur_w))
+            if cached and max_base:
+                bw = max_base
             base, bl = _rows(ctx, tag + "base", [series[i][4] for i in idx], bw)
         mt = np.array([metric_type_id(series[i][1], type_names) for i in idx], np.uint8)
+        extra = {}
+        if cached:
+            extra["row_ids"] = np.array([row_id(docs[series[i][0]]["id"], series[i][1]) for i in idx], np.uint64)
         r = ctx.score(cur, base, hist, strategy=A.FM_STRAT_CANARY if canary else A.FM_STRAT_HISTORICAL,
-                      cur_len=cl, base_len=bl, hist_len=hl, metric_type=mt)
+                      cur_len=cl, base_len=bl, hist_len=hl, metric_type=mt, **extra)
         for j, i in enumerate(idx):
             out[i] = r["rec"][j].copy()
     # per document: A.9 roll-up over its metrics, reason, anomalyInfo (models.go:60-63;
@@ -543,6 +567,14 @@ class BrainWorker:
         self.type_names = names
         ctx.set_params(g, table)
         self.errors = []          # (doc id, message) of write-backs that failed
+        # MAX_CACHE_SIZE ("max cached model size", foremast-brain/README.md:30): that many metric rows
+        # (baseline + history) stay in HBM between polls; rows are packed to fixed widths then
+        self.base_width = int(env.get("ML_BASELINE_POINTS", "1440"))
+        self.hist_width = int(env.get("ML_HISTORICAL_POINTS", "10080"))
+        self.cache_rows = int(env.get("MAX_CACHE_SIZE", "0"))
+        self.cached = self.cache_rows > 0 and hasattr(ctx, "cache_configure")
+        if self.cached:
+            ctx.cache_configure(self.cache_rows * 4 * (A.row_pitch(self.base_width) + A.row_pitch(self.hist_width)))
 
     def _stamp(self):
         return format_go_time(self.now())
@@ -581,7 +613,7 @@ class BrainWorker:
         docs = self.claim()
         if not docs:
             return {}
-        series, failed = fetch_documents(docs, self.fetch)
+        series, failed = fetch_documents(docs, self.fetch, self.ctx.cache_query if self.cached else None)
         live = []
         for d in docs:
             if d["id"] in failed:
@@ -593,7 +625,8 @@ class BrainWorker:
         keep = {id(d) for d in live}
         index = {i: j for j, i in enumerate(i for i, d in enumerate(docs) if id(d) in keep)}
         series = [(index[s[0]],) + tuple(s[1:]) for s in series if s[0] in index]
-        res = score_series(self.ctx, live, series, None, self.type_names)
+        res = score_series(self.ctx, live, series, None, self.type_names, max_hist=self.hist_width,
+                           max_base=self.base_width if self.cached else None, cached=self.cached)
         now = self.now()
         for d in live:
             r = res[d["id"]]

@@ -81,7 +81,8 @@ struct fm_ctx {
   FmParamsDev* d_params = nullptr;
   // staging for fm_score_batch: two chunk slots
   Arena in[2], out[2], roll, misc, hw;
-  RowCache cache;
+  RowCache cache[2];               // one per row layout (canary rows, history-only rows)
+  uint64_t cache_tick = 0, cache_used[2] = {0, 0};
   cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
   std::vector<cudaEvent_t> kev;    // per-chunk kernel timing events
   int score_smem_set = 0, groups_smem_set = 0, sort_smem_set = 0, elect_smem_set = 0, count_smem_set = 0;
@@ -514,7 +515,7 @@ int32_t fm_ctx_destroy(fm_ctx* c) {
     if (c->out_free[i]) cudaEventDestroy(c->out_free[i]);
   }
   for (cudaEvent_t e : c->kev) cudaEventDestroy(e);
-  c->roll.release(); c->misc.release(); c->hw.release(); c->cache.release();
+  c->roll.release(); c->misc.release(); c->hw.release(); c->cache[0].release(); c->cache[1].release();
   if (c->d_params) cudaFree(c->d_params);
   if (c->ev_a) cudaEventDestroy(c->ev_a);
   if (c->ev_b) cudaEventDestroy(c->ev_b);
@@ -628,15 +629,25 @@ namespace {
 
 // (Re)build the cache storage for this batch's row layout.  Returns false when the cache is off or
 // cannot hold a single row.
-int32_t cache_prepare(fm_ctx* c, const fm_batch* b, bool canary, bool* on) {
-  RowCache& k = c->cache;
-  *on = false;
-  if (k.max_bytes == 0) return FM_OK;
+int32_t cache_prepare(fm_ctx* c, const fm_batch* b, bool canary, RowCache** on) {
+  *on = nullptr;
+  if (c->cache[0].max_bytes == 0) return FM_OK;
   const uint32_t nb = canary ? b->n_base : 0u, pb = canary ? b->base_pitch : 0u;
   const uint32_t nh = b->hist ? b->n_hist : 0u, ph = b->hist ? b->hist_pitch : 0u;
   const uint64_t row_bytes = 4ull * ((uint64_t)pb + ph);
   if (row_bytes == 0) return FM_OK;                       // nothing cacheable in this batch
-  if (k.cap && (k.n_base != nb || k.base_pitch != pb || k.n_hist != nh || k.hist_pitch != ph)) k.release();
+  // the cache of this layout; else an unused one; else the one that was used longest ago
+  int which = -1;
+  for (int i = 0; i < 2; ++i) {
+    const RowCache& q = c->cache[i];
+    if (q.cap && q.n_base == nb && q.base_pitch == pb && q.n_hist == nh && q.hist_pitch == ph) which = i;
+  }
+  if (which < 0) {
+    which = !c->cache[0].cap ? 0 : (!c->cache[1].cap ? 1 : (c->cache_used[0] <= c->cache_used[1] ? 0 : 1));
+    c->cache[which].release();
+  }
+  RowCache& k = c->cache[which];
+  c->cache_used[which] = ++c->cache_tick;
   if (!k.cap) {
     const uint64_t cap = std::min<uint64_t>(k.max_bytes / row_bytes, 0xFFFFFFF0ull);
     if (cap == 0) return FM_OK;
@@ -650,7 +661,7 @@ int32_t cache_prepare(fm_ctx* c, const fm_batch* b, bool canary, bool* on) {
     k.slot_live.assign(cap, 0);
     k.index.reserve((size_t)std::min<uint64_t>(cap, 1u << 22));
   }
-  *on = true;
+  *on = &k;
   return FM_OK;
 }
 
@@ -741,15 +752,16 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
   const size_t rsz = rec_size(b->record_kind);
 
   // row cache: slot per row, which rows still have to come over PCIe
-  bool cached = false;
+  RowCache* kcp = nullptr;
   std::vector<uint32_t> slot;
   std::vector<uint8_t> miss;
   std::vector<uint32_t> eff_blen, eff_hlen;
   if (row_ids) {
-    rc = cache_prepare(c, b, canary, &cached);
+    rc = cache_prepare(c, b, canary, &kcp);
     if (rc != FM_OK) return rc;
   }
-  RowCache& kc = c->cache;
+  const bool cached = kcp != nullptr;
+  RowCache& kc = cached ? *kcp : c->cache[0];
   if (cached) {
     cache_assign(kc, b, row_ids, S, canary, slot, miss);
     // lengths: a resident row keeps the length it was stored with
@@ -959,26 +971,38 @@ int32_t fm_cache_configure(fm_ctx* c, uint64_t max_bytes) {
   if (!c) return FM_E_INVALID;
   FM_CK(c, cudaSetDevice(c->device));
   FM_CK(c, cudaStreamSynchronize(c->stream));
-  c->cache.release();
-  c->cache.max_bytes = max_bytes;
-  c->cache.hits = c->cache.misses = c->cache.evictions = c->cache.uncached = 0;
+  for (int i = 0; i < 2; ++i) {
+    RowCache& k = c->cache[i];
+    k.release();
+    k.max_bytes = max_bytes;
+    k.hits = k.misses = k.evictions = k.uncached = 0;
+  }
   return FM_OK;
 }
 
 int32_t fm_cache_get_stats(fm_ctx* c, fm_cache_stats* out) {
   if (!c || !out) return FM_E_INVALID;
-  const RowCache& k = c->cache;
-  out->max_bytes = k.max_bytes; out->capacity_rows = k.cap; out->resident_rows = k.n_live;
-  out->hits = k.hits; out->misses = k.misses; out->evictions = k.evictions; out->uncached = k.uncached;
-  out->row_bytes = 4ull * ((uint64_t)k.base_pitch + k.hist_pitch);
+  memset(out, 0, sizeof(*out));
+  out->max_bytes = c->cache[0].max_bytes;
+  for (int i = 0; i < 2; ++i) {
+    const RowCache& k = c->cache[i];
+    out->capacity_rows += k.cap; out->resident_rows += k.n_live;
+    out->hits += k.hits; out->misses += k.misses; out->evictions += k.evictions; out->uncached += k.uncached;
+    out->row_bytes = std::max<uint64_t>(out->row_bytes, 4ull * ((uint64_t)k.base_pitch + k.hist_pitch));
+  }
   return FM_OK;
 }
 
 int32_t fm_cache_query(fm_ctx* c, const uint64_t* row_ids, uint64_t n, uint8_t* resident_out) {
   if (!c) return FM_E_INVALID;
   if (n && (!row_ids || !resident_out)) return fail(c, FM_E_INVALID, "fm_cache_query: null pointer");
-  const RowCache& k = c->cache;
-  for (uint64_t i = 0; i < n; ++i) resident_out[i] = k.cap && k.index.find(row_ids[i]) != k.index.end() ? 1 : 0;
+  for (uint64_t i = 0; i < n; ++i) {
+    resident_out[i] = 0;
+    for (int q = 0; q < 2; ++q) {
+      const RowCache& k = c->cache[q];
+      if (k.cap && k.index.find(row_ids[i]) != k.index.end()) resident_out[i] = 1;
+    }
+  }
   return FM_OK;
 }
 

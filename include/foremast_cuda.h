@@ -304,8 +304,10 @@ int32_t fm_score_batch(fm_ctx* ctx, const fm_batch* batch, void* out_records,
  *                     are uploaded every call.  A resident row keeps the length
  *                     it was stored with (pass base_len / hist_len on every call
  *                     if any row is ragged).  Results are identical to
- *                     fm_score_batch on the same rows.  One row layout (n_base,
- *                     base_pitch, n_hist, hist_pitch) is resident at a time.
+ *                     fm_score_batch on the same rows.  Two row layouts (n_base,
+ *                     base_pitch, n_hist, hist_pitch) are resident at a time — the
+ *                     canary rows and the history-only rows of a poll — each within
+ *                     max_bytes; a third layout replaces the one used longest ago.
  * fm_cache_query      resident_out[i] = 1 if row_ids[i] is resident.
  * fm_cache_get_stats  counters since fm_cache_configure. */
 typedef struct {

@@ -95,12 +95,19 @@ def test_ragged_rows_history_and_layout_change():
             got = ctx.score(cur, base, hist, metric_type=mt, base_len=bl, hist_len=hl, row_ids=ids)["rec"]
             assert got.tobytes() == ref.tobytes()
             bl, hl = np.zeros_like(bl), np.zeros_like(hl)
-        # historical strategy (no baseline) is another layout: the cache starts afresh
+        # historical strategy (no baseline) is another layout: it gets the second cache, the canary
+        # rows stay resident beside it (a poll of mixed jobs alternates between the two)
         ref2 = ctx.score(cur, None, hist, strategy=A.FM_STRAT_HISTORICAL, metric_type=mt)["rec"]
         for _ in range(2):
             got2 = ctx.score(cur, None, hist, strategy=A.FM_STRAT_HISTORICAL, metric_type=mt, row_ids=ids)["rec"]
             assert got2.tobytes() == ref2.tobytes()
-        assert ctx.cache_stats()["resident_rows"] == S
+        assert ctx.cache_stats()["resident_rows"] == 2 * S
+        hits = ctx.cache_stats()["hits"]
+        got = ctx.score(cur, base, hist, metric_type=mt, base_len=bl, hist_len=hl, row_ids=ids)["rec"]
+        assert got.tobytes() == ref.tobytes() and ctx.cache_stats()["hits"] == hits + S
+        # a third layout replaces the one used longest ago (the history-only one)
+        ctx.score(cur, base[:, :100], None, metric_type=mt, row_ids=ids)
+        assert ctx.cache_query(ids[:3]).all() and ctx.cache_stats()["resident_rows"] == 2 * S
 
 
 def test_cached_multi_chunk_with_rollup():
