@@ -10,6 +10,16 @@
 // 2 R_k = sum over the group's points of (lower + upper + 1).
 // Services with more than 8 groups are appended to a list that k_score_groups (the general
 // shared-memory kernel, fm_kernels.cu) works off afterwards.
+//
+// Heavy ties first: the rollover metrics are error counts per scrape interval, a pooled sample of
+// 180-480 points with a handful of distinct values.  Before sorting anything the warp builds the
+// multiset of the sample in a 256-slot hash table in its parking buffer (election: every key stores
+// its bits into its slot if it read it empty, whoever reads its own bits back owns the slot and
+// counts itself with a fire-and-forget shared-memory add; the others try the next multiplier).  With
+// D <= 32 distinct values, one per lane, "points below me" is a D-step loop over the (value, count)
+// list, which gives 2 * midrank and t^3 - t per value, and every point fetches the midrank of its
+// value from its slot: ~0.5k instructions where sort + park + two searches per point take 2.7k.
+// A sample with more distinct values (or four failed rounds) takes the network: same integers.
 #include <cstdint>
 #include <cuda_runtime.h>
 #include <math_constants.h>
@@ -32,6 +42,127 @@ constexpr int kWarps = 32;        // one CTA per SM: all its warps walk the code
 
 __device__ __forceinline__ uint32_t row_len(const uint32_t* len, uint64_t s, uint32_t n) {
   return len ? min(__ldg(len + s), n) : n;
+}
+
+constexpr uint32_t kSlots = 256u;         // hash slots per warp: values at +0, counts / midranks at +4*kSlots
+constexpr uint32_t kEmpty = 0xFFFFFFFFu;   // a NaN pattern: rows are NaN-free (foremast_cuda.h)
+constexpr int kRounds = 4;
+static_assert(2u * kSlots * 4u <= 32u * kR * 4u, "the table lives in the warp's parking buffer");
+
+__device__ __forceinline__ uint32_t slot_of(uint32_t tbl_s, float key, uint32_t mult) {
+  return tbl_s + (((__float_as_uint(key) * mult) >> 24) << 2);
+}
+
+// 2 * (rank sum) of group k into lane k and the tie term, from the multiset of the pooled sample.
+// s[2k], s[2k+1]: the points lane and lane + 32 of group k (-0 folded into +0), valid: bit r = s[r]
+// is a point.  Destroys s.  False: more than 32 distinct values or unplaced keys; nothing returned.
+__device__ __forceinline__ bool ranks_by_multiset(float (&s)[kR], const uint32_t valid, const uint32_t K, const int lane,
+                                                  const uint32_t tbl_s, uint32_t& r2_mine, long long& T) {
+  __syncwarp();
+  {
+    const uint32_t z = tbl_s + (uint32_t)lane * 32u;
+    const float e = __uint_as_float(kEmpty);
+    fm_sts_v4(z, e, e, e, e); fm_sts_v4(z + 16u, e, e, e, e);
+    fm_sts_v4(z + 4u * kSlots, 0.f, 0.f, 0.f, 0.f); fm_sts_v4(z + 4u * kSlots + 16u, 0.f, 0.f, 0.f, 0.f);
+  }
+  __syncwarp();
+  uint32_t pend = valid;
+#pragma unroll 1
+  for (int round = 0; round < kRounds; ++round) {
+    if (!__any_sync(FM_FULL, pend != 0u)) break;
+    const uint32_t mult = 0x9E3779B1u + 0x3C6EF372u * (uint32_t)round;   // odd
+#pragma unroll
+    for (int k = 0; k < kGroups; ++k) {
+      if ((uint32_t)k < K) {                       // warp-uniform
+#pragma unroll
+        for (int r = 2 * k; r < 2 * k + 2; ++r) {
+          if (pend & (1u << r)) {
+            const uint32_t a = slot_of(tbl_s, s[r], mult);
+            if (fm_lds_u32(a) == kEmpty) fm_sts_f32(a, s[r]);
+          }
+        }
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < kGroups; ++k) {
+      if ((uint32_t)k < K) {
+#pragma unroll
+        for (int r = 2 * k; r < 2 * k + 2; ++r) {
+          if (pend & (1u << r)) {
+            const uint32_t a = slot_of(tbl_s, s[r], mult);
+            if (fm_lds_u32(a) == __float_as_uint(s[r])) {
+              fm_reds_add(a + 4u * kSlots, 1u);
+              s[r] = __uint_as_float(a + 4u * kSlots);   // from here on: where my value's midrank will be
+              pend &= ~(1u << r);
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  }
+  if (__any_sync(FM_FULL, pend != 0u)) return false;
+
+  // the occupied slots, 8 per lane, into a dense (value, count | slot) list
+  const uint32_t mine_s = tbl_s + (uint32_t)lane * 32u;
+  const float4 va = fm_lds_v4(mine_s), vb = fm_lds_v4(mine_s + 16u);
+  const float4 ca = fm_lds_v4(mine_s + 4u * kSlots), cb = fm_lds_v4(mine_s + 4u * kSlots + 16u);
+  const float vv[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
+  const uint32_t cc[8] = {__float_as_uint(ca.x), __float_as_uint(ca.y), __float_as_uint(ca.z), __float_as_uint(ca.w),
+                          __float_as_uint(cb.x), __float_as_uint(cb.y), __float_as_uint(cb.z), __float_as_uint(cb.w)};
+  uint32_t occ = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) occ += cc[j] ? 1u : 0u;
+  uint32_t incl = occ;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t u = __shfl_up_sync(FM_FULL, incl, o);
+    if (lane >= o) incl += u;
+  }
+  const uint32_t D = __shfl_sync(FM_FULL, incl, 31);
+  if (D > 32u) return false;
+  __syncwarp();                                    // every lane holds its slots: the value half becomes the list
+  uint32_t at = tbl_s + (incl - occ) * 8u;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (cc[j]) {
+      fm_sts_f32(at, vv[j]);
+      fm_sts_u32(at + 4u, cc[j] | (((uint32_t)lane * 8u + (uint32_t)j) << 16));
+      at += 8u;
+    }
+  }
+  __syncwarp();
+  float dv = 0.f;
+  uint32_t dc = 0, dslot = 0;
+  if ((uint32_t)lane < D) {
+    dv = fm_lds_f32(tbl_s + (uint32_t)lane * 8u);
+    const uint32_t w = fm_lds_u32(tbl_s + (uint32_t)lane * 8u + 4u);
+    dc = w & 0xFFFFu; dslot = w >> 16;
+  }
+  uint32_t less = 0;
+#pragma unroll 2
+  for (uint32_t i = 0; i < D; ++i) {               // broadcast reads
+    const float vi = fm_lds_f32(tbl_s + i * 8u);
+    const uint32_t ci = fm_lds_u32(tbl_s + i * 8u + 4u) & 0xFFFFu;
+    less += (vi < dv) ? ci : 0u;
+  }
+  T = (long long)__reduce_add_sync(FM_FULL, dc * (dc * dc - 1u));   // sum t^3 - t <= 512^3
+  if ((uint32_t)lane < D) fm_sts_u32(tbl_s + 4u * kSlots + dslot * 4u, 2u * less + dc + 1u);
+  __syncwarp();
+  r2_mine = 0;
+#pragma unroll
+  for (int k = 0; k < kGroups; ++k) {
+    if ((uint32_t)k < K) {
+      uint32_t m = 0;
+      if (valid & (1u << (2 * k))) m = fm_lds_u32(__float_as_uint(s[2 * k]));
+      if (valid & (2u << (2 * k))) m += fm_lds_u32(__float_as_uint(s[2 * k + 1]));
+      m = __reduce_add_sync(FM_FULL, m);
+      if (lane == k) r2_mine = m;
+    }
+  }
+  __syncwarp();
+  return true;
 }
 
 __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a, uint32_t* defer_list, uint32_t* defer_n) {
@@ -112,9 +243,9 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
       if (differ) status_kw |= FM_ST_DIFFER;
     }
     if (want_kw) {
-      // groups into registers (the sort does not care which key sits where)
+      // groups into registers (neither path cares which key sits where)
       float s[kR];
-      uint32_t N = 0;
+      uint32_t N = 0, valid = 0, n_mine = 1;
       bool eligible = K >= 2;
 #pragma unroll
       for (int k = 0; k < kGroups; ++k) {
@@ -122,36 +253,51 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
         if ((uint32_t)k < K) {
           const uint32_t n = row_len(a.cur_len, g0 + k, a.n_cur);
           const float* row = a.cur + (uint64_t)(g0 + k) * a.cur_pitch;
-          if ((uint32_t)lane < n) s[2 * k] = __ldg(row + lane) + 0.0f;            // -0 -> +0
-          if ((uint32_t)lane + 32u < n) s[2 * k + 1] = __ldg(row + lane + 32) + 0.0f;
+          if ((uint32_t)lane < n) { s[2 * k] = __ldg(row + lane) + 0.0f; valid |= 1u << (2 * k); }            // -0 -> +0
+          if ((uint32_t)lane + 32u < n) { s[2 * k + 1] = __ldg(row + lane + 32) + 0.0f; valid |= 2u << (2 * k); }
           N += n;
+          if (lane == k) n_mine = n;
           if (n < g.min_kw || n == 0) eligible = false;
         }
       }
       if (eligible) {
-        sort_rows<kR, kR>(s, lane, park_s);
-        long long T = (long long)tie_term_and_park<kR>(s, N, lane, park_s);
-        T = fm_warp_sum(T);
-        double sres = 0.0;
-#pragma unroll 1
-        for (uint32_t k = 0; k < K; ++k) {
-          const uint32_t n = row_len(a.cur_len, g0 + k, a.n_cur);
-          const float* row = a.cur + (uint64_t)(g0 + k) * a.cur_pitch;
-          long long r2 = 0;
-#pragma unroll 1
-          for (uint32_t i = lane; i < n; i += 32) {
-            const float q = __ldg(row + i) + 0.0f;
-            r2 += (long long)(parked_lower<kR>(park_s, N, q) + parked_upper<kR>(park_s, N, q) + 1u);
+        uint32_t r2_mine = 0;                      // lane k: twice the rank sum of group k
+        long long T = 0;
+        if (!ranks_by_multiset(s, valid, K, lane, park_s, r2_mine, T)) {
+#pragma unroll
+          for (int k = 0; k < kGroups; ++k) {      // the keys again (L1)
+            s[2 * k] = CUDART_INF_F; s[2 * k + 1] = CUDART_INF_F;
+            if ((uint32_t)k < K) {
+              const float* row = a.cur + (uint64_t)(g0 + k) * a.cur_pitch;
+              if (valid & (1u << (2 * k))) s[2 * k] = __ldg(row + lane) + 0.0f;
+              if (valid & (2u << (2 * k))) s[2 * k + 1] = __ldg(row + lane + 32) + 0.0f;
+            }
           }
-          r2 = fm_warp_sum(r2);
-          const double R = 0.5 * (double)r2;
-          sres += R * R / (double)n;
+          sort_rows<kR, kR>(s, lane, park_s);
+          T = (long long)tie_term_and_park<kR>(s, N, lane, park_s);
+          T = fm_warp_sum(T);
+#pragma unroll 1
+          for (uint32_t k = 0; k < K; ++k) {
+            const uint32_t n = row_len(a.cur_len, g0 + k, a.n_cur);
+            const float* row = a.cur + (uint64_t)(g0 + k) * a.cur_pitch;
+            uint32_t r2 = 0;
+#pragma unroll 1
+            for (uint32_t i = lane; i < n; i += 32) {
+              const float q = __ldg(row + i) + 0.0f;
+              r2 += parked_lower<kR>(park_s, N, q) + parked_upper<kR>(park_s, N, q) + 1u;
+            }
+            r2 = __reduce_add_sync(FM_FULL, r2);
+            if ((uint32_t)lane == k) r2_mine = r2;
+          }
+          __syncwarp();
         }
+        // sum R_k^2 / n_k: one division for all groups
+        const double R = 0.5 * (double)r2_mine;
+        const double sres = fm_warp_sum((uint32_t)lane < K ? R * R / (double)n_mine : 0.0);
         kw = fm_kruskal(sres, (double)N, T, K);
         status_kw |= FM_ST_KW_RUN;
         if (kw.degenerate) status_kw |= FM_ST_DEGENERATE;
         else differ = kw.p < g.alpha;
-        __syncwarp();
       }
       if (!(status_kw & FM_ST_KW_RUN) || kw.degenerate) status_kw |= FM_ST_PAIRWISE_SKIPPED;
       if (differ) status_kw |= FM_ST_DIFFER;
@@ -162,25 +308,32 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
     const double up = __dadd_rn(mean, __dmul_rn(kk, sigma));
     double lo = __dsub_rn(mean, __dmul_rn(kk, sigma));
     if (lo < tp.min_lower_bound) lo = tp.min_lower_bound;
-    const bool chk_up = (tp.bound_mask & 1u) != 0, chk_lo = (tp.bound_mask & 2u) != 0;
+    // fp32 points against fp64 bounds, exactly: x > up <=> x > rd(up), x < lo <=> x < ru(lo) (fm_ma.cu)
+    const float up_f = (tp.bound_mask & 1u) ? __double2float_rd(up) : CUDART_INF_F;
+    const float lo_f = (tp.bound_mask & 2u) ? __double2float_ru(lo) : -CUDART_INF_F;
+    uint32_t ba_mine = 0, bb_mine = 0, nc_mine = 0;     // lane k: flags and length of group k
 #pragma unroll 1
     for (uint32_t k = 0; k < K; ++k) {
+      const uint32_t nc = row_len(a.cur_len, g0 + k, a.n_cur);
+      const float* row = a.cur + (uint64_t)(g0 + k) * a.cur_pitch;
+      const float xa = (uint32_t)lane < nc ? __ldg(row + lane) : 0.f;
+      const float xb = (uint32_t)lane + 32u < nc ? __ldg(row + lane + 32) : 0.f;
+      const bool fa = model_ok && (uint32_t)lane < nc && (xa > up_f || xa < lo_f);
+      const bool fb = model_ok && (uint32_t)lane + 32u < nc && (xb > up_f || xb < lo_f);
+      const uint32_t ba = __ballot_sync(FM_FULL, fa), bb = __ballot_sync(FM_FULL, fb);
+      if ((uint32_t)lane == k) { ba_mine = ba; bb_mine = bb; nc_mine = nc; }
+    }
+    uint32_t verdict = 0xFFu;
+    if ((uint32_t)lane < K) {                      // lane k writes the record of group k
       fm_series_rec rec;
       fm_rec_init(rec);
       rec.h = kw.stat; rec.p_h = kw.p; rec.mean = mean; rec.sigma = sigma;
       uint32_t status = status_kw;
-      const uint32_t nc = row_len(a.cur_len, g0 + k, a.n_cur);
-      const float* row = a.cur + (uint64_t)(g0 + k) * a.cur_pitch;
       if (!model_ok) status |= FM_ST_HIST_INSUFFICIENT;
-      if (nc == 0) status |= FM_ST_NO_CURRENT;
-      if (model_ok && nc > 0) {
-        const double xa = (uint32_t)lane < nc ? (double)__ldg(row + lane) : 0.0;
-        const double xb = (uint32_t)lane + 32u < nc ? (double)__ldg(row + lane + 32) : 0.0;
-        const bool fa = (uint32_t)lane < nc && ((chk_up && xa > up) || (chk_lo && xa < lo));
-        const bool fb = (uint32_t)lane + 32u < nc && ((chk_up && xb > up) || (chk_lo && xb < lo));
-        const uint32_t ba = __ballot_sync(FM_FULL, fa), bb = __ballot_sync(FM_FULL, fb);
-        const uint64_t mask = (uint64_t)ba | ((uint64_t)bb << 32);
-        const uint32_t cnt = (uint32_t)__popc(ba) + (uint32_t)__popc(bb);
+      if (nc_mine == 0) status |= FM_ST_NO_CURRENT;
+      if (model_ok && nc_mine > 0) {
+        const uint64_t mask = (uint64_t)ba_mine | ((uint64_t)bb_mine << 32);
+        const uint32_t cnt = (uint32_t)__popc(ba_mine) + (uint32_t)__popc(bb_mine);
         rec.upper = up; rec.lower = lo;
         rec.n_anom = cnt;
         rec.first_idx = (uint16_t)(mask ? (uint32_t)__ffsll((long long)mask) - 1u : 0xFFFFu);
@@ -189,9 +342,16 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
       }
       if (status & (FM_ST_NO_CURRENT | FM_ST_HIST_INSUFFICIENT)) rec.verdict = FM_UNKNOWN;
       rec.status = (uint8_t)status;
+      verdict = rec.verdict;
+      a.out[g0 + lane] = rec;
+    }
+    if (a.svc) {                                    // one warp owns the service: one add per counter
+      const uint32_t bad = __popc(__ballot_sync(FM_FULL, verdict == FM_UNHEALTHY));
+      const uint32_t unk = __popc(__ballot_sync(FM_FULL, verdict == FM_UNKNOWN));
       if (lane == 0) {
-        a.out[g0 + k] = rec;
-        if (a.svc) fm_rollup_add(a.svc, (uint32_t)v, 0xFFFFFFFFu, rec.verdict);
+        atomicAdd(&a.svc[v].n_children, K);
+        if (bad) atomicAdd(&a.svc[v].n_unhealthy, bad);
+        if (unk) atomicAdd(&a.svc[v].n_unknown, unk);
       }
     }
     __syncwarp();

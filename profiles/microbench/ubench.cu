@@ -55,6 +55,18 @@ __global__ void __launch_bounds__(256) probe(uint32_t* out, uint32_t seed, long 
         const uint4 v = reinterpret_cast<const uint4*>(sm)[(a + u) & 1023]; a = v.x + v.w;
       } else if (OP == 14) {   // REDUX (warp reduce add)
         a += __reduce_add_sync(0xffffffffu, a + u);
+      } else if (OP == 15) {   // ATOMS.ADD, the 32 lanes of a warp on ONE address (heavy ties)
+        atomicAdd(&sm[((tid >> 5) * 64 + u) & 4095], 1u);
+      } else if (OP == 16) {   // ATOMS.ADD, 4 addresses per warp
+        atomicAdd(&sm[((tid >> 5) * 64 + u * 4 + (lane & 3)) & 4095], 1u);
+      } else if (OP == 17) {   // ATOMS.CAS, one address per warp
+        a += atomicCAS(&sm[((tid >> 5) * 64 + u) & 4095], a, b);
+      } else if (OP == 18) {   // ATOMS.CAS random address
+        a += atomicCAS(&sm[(a + u * 977) & 4095], a, b); a = a * 1664525u + 1013904223u;
+      } else if (OP == 19) {   // STS of one value to one address from every lane, then LDS of it (election)
+        sm[((tid >> 5) * 64 + u) & 4095] = a; a += sm[((tid >> 5) * 64 + u) & 4095];
+      } else if (OP == 20) {   // ATOMS.ADD returning, one address per warp
+        a += atomicAdd(&sm[((tid >> 5) * 64 + u) & 4095], 1u);
       }
     }
   }
@@ -101,5 +113,11 @@ int main() {
   run<12>("imad + shf", 2, out, clk);
   run<13>("lds.128 random", 1, out, clk);
   run<14>("redux.add", 1, out, clk);
+  run<15>("atoms.add one address per warp", 1, out, clk);
+  run<16>("atoms.add 4 addresses per warp", 1, out, clk);
+  run<17>("atoms.cas one address per warp", 1, out, clk);
+  run<18>("atoms.cas random", 1, out, clk);
+  run<19>("sts + lds one address per warp", 2, out, clk);
+  run<20>("atoms.add (returning) one address", 1, out, clk);
   return 0;
 }
