@@ -70,8 +70,8 @@ def lib():
     """Load (building first if the sources are newer) libforemast_cuda.so."""
     global _lib
     if _lib is None:
-        path = _build.SO
-        if _build.stale():
+        path = os.environ.get("FOREMAST_CUDA_LIB") or _build.SO   # override: an already built library (kernel variants)
+        if path == _build.SO and _build.stale():
             try:
                 _build.build()
             except Exception as e:  # no nvcc on this machine: use the shipped .so if any

@@ -1057,8 +1057,10 @@ int32_t fm_score_groups_device(fm_ctx* c, const fm_group_batch* b, fm_series_rec
     uint32_t* d_list = static_cast<uint32_t*>(c->misc.p);
     uint32_t* d_cnt = reinterpret_cast<uint32_t*>(static_cast<char*>(c->misc.p) + al_n);
     FM_CK(c, cudaMemsetAsync(d_cnt, 0, 4, c->stream));
-    const uint64_t need = (b->n_services + 31) / 32;               // 32 warps per CTA, one CTA per SM
-    const int g_fast = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms, need));
+    int gw = 32, gc = 1;                                           // persistent grid: warps per CTA, CTAs per SM
+    fm_groups_sort_shape(&gw, &gc);
+    const uint64_t need = (b->n_services + gw - 1) / gw;
+    const int g_fast = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * gc, need));
     launches += fm_launch_groups_sort(a, d_list, d_cnt, g_fast, c->stream);
     a.list = d_list; a.list_n = d_cnt;
     launches += fm_launch_groups(a, wpc, std::min(grid, c->num_sms), c->stream);

@@ -195,7 +195,6 @@ __device__ __forceinline__ void fm_moments_finish(FmMom m, double pivot, uint32_
 __device__ __forceinline__ void fm_moments_global(const float* __restrict__ x, uint32_t n,
                                                   uint32_t ddof, int lane, double& mean,
                                                   double& sigma) {
-  const double pivot = (double)__ldg(x);
   FmMom m = {0.0, 0.0};
   const uint32_t n4 = n >> 2;
   const float4* x4 = reinterpret_cast<const float4*>(x);
@@ -207,6 +206,9 @@ __device__ __forceinline__ void fm_moments_global(const float* __restrict__ x, u
     q[j] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (lane + 32u * j < n4) q[j] = fm_ldg_stream(x4 + lane + 32u * j);
   }
+  // pivot = x[0]: lane 0 holds it in its first vector (no load of its own in front of the stream)
+  const float p0 = __shfl_sync(FM_FULL, q[0].x, 0);
+  const double pivot = (double)(n4 ? p0 : __ldg(x));
   for (uint32_t i = lane; i < n4; i += 128) {
     float4 r[4];
 #pragma unroll

@@ -21,6 +21,7 @@
 // value from its slot: ~0.5k instructions where sort + park + two searches per point take 2.7k.
 // A sample with more distinct values (or four failed rounds) takes the network: same integers.
 #include <cstdint>
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
@@ -28,7 +29,7 @@
 #include "fm_sortnet.cuh"
 
 #ifndef FM_GROUPS_SYNC
-#define FM_GROUPS_SYNC 1
+#define FM_GROUPS_SYNC 2
 #endif
 
 namespace {
@@ -38,7 +39,17 @@ constexpr int kGroups = 8;        // groups held in registers
 constexpr int kR = 2 * kGroups;   // keys per lane
 constexpr uint32_t kSyncEvery = FM_GROUPS_SYNC;   // services between two CTA barriers (power of two)
 constexpr bool kSyncTwice = false;  // second barrier between the history stream and the rank stage
-constexpr int kWarps = 32;        // one CTA per SM: all its warps walk the code together
+#ifndef FM_GROUPS_WARPS
+#define FM_GROUPS_WARPS 20
+#endif
+#ifndef FM_GROUPS_EARLY
+#define FM_GROUPS_EARLY 1
+#endif
+#ifndef FM_GROUPS_CTAS
+#define FM_GROUPS_CTAS 1
+#endif
+constexpr int kCtas = FM_GROUPS_CTAS;     // CTAs per SM
+constexpr int kWarps = FM_GROUPS_WARPS;   // one CTA per SM: all its warps walk the code together
 
 __device__ __forceinline__ uint32_t row_len(const uint32_t* len, uint64_t s, uint32_t n) {
   return len ? min(__ldg(len + s), n) : n;
@@ -55,7 +66,7 @@ __device__ __forceinline__ uint32_t slot_of(uint32_t tbl_s, float key, uint32_t 
 
 // 2 * (rank sum) of group k into lane k and the tie term, from the multiset of the pooled sample.
 // s[2k], s[2k+1]: the points lane and lane + 32 of group k (-0 folded into +0), valid: bit r = s[r]
-// is a point.  Destroys s.  False: more than 32 distinct values or unplaced keys; nothing returned.
+// is a point, otherwise a copy of some point of the group.  Destroys s.  False: more than 32 distinct values or unplaced keys; nothing returned.
 __device__ __forceinline__ bool ranks_by_multiset(float (&s)[kR], const uint32_t valid, const uint32_t K, const int lane,
                                                   const uint32_t tbl_s, uint32_t& r2_mine, long long& T) {
   __syncwarp();
@@ -66,9 +77,37 @@ __device__ __forceinline__ bool ranks_by_multiset(float (&s)[kR], const uint32_t
     fm_sts_v4(z + 4u * kSlots, 0.f, 0.f, 0.f, 0.f); fm_sts_v4(z + 4u * kSlots + 16u, 0.f, 0.f, 0.f, 0.f);
   }
   __syncwarp();
-  uint32_t pend = valid;
+  // round 0, straight line: the table is empty, so every key stores (a lane behind the end of its
+  // group holds a copy of one of the group's points: its stores change nothing and it never counts)
+  uint32_t pend = 0;
+  {
+    constexpr uint32_t mult = 0x9E3779B1u;
+#pragma unroll
+    for (int k = 0; k < kGroups; ++k) {
+      if ((uint32_t)k < K) {                       // warp-uniform
+        fm_sts_f32(slot_of(tbl_s, s[2 * k], mult), s[2 * k]);
+        fm_sts_f32(slot_of(tbl_s, s[2 * k + 1], mult), s[2 * k + 1]);
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < kGroups; ++k) {
+      if ((uint32_t)k < K) {
+#pragma unroll
+        for (int r = 2 * k; r < 2 * k + 2; ++r) {
+          const uint32_t a = slot_of(tbl_s, s[r], mult);
+          const bool won = fm_lds_u32(a) == __float_as_uint(s[r]);
+          const bool real = (valid >> r) & 1u;
+          if (won && real) fm_reds_add(a + 4u * kSlots, 1u);
+          if (!won && real) pend |= 1u << r;
+          s[r] = won ? __uint_as_float(a + 4u * kSlots) : s[r];
+        }
+      }
+    }
+    __syncwarp();
+  }
 #pragma unroll 1
-  for (int round = 0; round < kRounds; ++round) {
+  for (int round = 1; round < kRounds; ++round) {
     if (!__any_sync(FM_FULL, pend != 0u)) break;
     const uint32_t mult = 0x9E3779B1u + 0x3C6EF372u * (uint32_t)round;   // odd
 #pragma unroll
@@ -165,7 +204,8 @@ __device__ __forceinline__ bool ranks_by_multiset(float (&s)[kR], const uint32_t
   return true;
 }
 
-__global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a, uint32_t* defer_list, uint32_t* defer_n) {
+__global__ void __launch_bounds__(kWarps * 32, kCtas) k_groups_sort(const FmGArgs a, uint32_t* defer_list, uint32_t* defer_n,
+                                                                const uint32_t sync_mask) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -178,47 +218,79 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
   // loops (their values are re-read through L1): 24 warps per SM at unrelated places of a long
   // unrolled body starve on instruction fetch (measured: 17 warps stalled on it per issue).
   uint32_t round = 0;
+  uint32_t ng0 = 0, ng1 = 0, nty = 0;              // group range and metric type of the service this warp takes next
+  {
+    const uint64_t v = (uint64_t)blockIdx.x * wpc + warp;
+    if (v < a.n_services) {
+      ng0 = a.group_offsets[v]; ng1 = a.group_offsets[v + 1];
+      if (a.metric_type) nty = a.metric_type[v];
+    }
+  }
   for (uint64_t v0 = (uint64_t)blockIdx.x * wpc; v0 < a.n_services; v0 += (uint64_t)gridDim.x * wpc, ++round) {
-    if ((round & (kSyncEvery - 1u)) == 0u) __syncthreads();
+    if ((round & sync_mask) == 0u) __syncthreads();
     const uint64_t v = v0 + warp;
-    uint32_t g0 = 0, K = 0;
+    const uint32_t g0 = ng0, K = ng1 - ng0;
     bool active = v < a.n_services;
-    if (active) {
-      g0 = a.group_offsets[v];
-      K = a.group_offsets[v + 1] - g0;
-      if (K > (uint32_t)kGroups) {
-        if (lane == 0) defer_list[atomicAdd(defer_n, 1u)] = (uint32_t)v;
-        active = false;
-      }
+    const uint64_t vn = v + (uint64_t)gridDim.x * wpc;
+    const bool more = vn < a.n_services;
+    const uint32_t ty = nty;
+    if (more) {                                    // used after the model: no wait
+      ng0 = a.group_offsets[vn]; ng1 = a.group_offsets[vn + 1];
+      if (a.metric_type) nty = a.metric_type[vn];
+    }
+    if (active && K > (uint32_t)kGroups) {
+      if (lane == 0) defer_list[atomicAdd(defer_n, 1u)] = (uint32_t)v;
+      active = false;
     }
     fm_type_params tp = a.P->types[0];
     double mean = 0.0, sigma = 0.0;
     bool model_ok = false;
+    float s[kR];                                   // group k: points lane and lane + 32 in s[2k], s[2k+1]
+    uint32_t N = 0, valid = 0, n_mine = 1;
+    bool eligible = K >= 2;
+    auto load_points = [&]() {
+#pragma unroll
+      for (int k = 0; k < kGroups; ++k) {
+        s[2 * k] = CUDART_INF_F; s[2 * k + 1] = CUDART_INF_F;
+        if ((uint32_t)k < K) {
+          const uint32_t n = row_len(a.cur_len, g0 + k, a.n_cur);
+          const float* row = a.cur + (uint64_t)(g0 + k) * a.cur_pitch;
+          if (n) {                                  // behind the row's end: a copy of its last point
+            s[2 * k] = __ldg(row + min((uint32_t)lane, n - 1u));
+            s[2 * k + 1] = __ldg(row + min((uint32_t)lane + 32u, n - 1u));
+          }
+          if ((uint32_t)lane < n) valid |= 1u << (2 * k);
+          if ((uint32_t)lane + 32u < n) valid |= 2u << (2 * k);
+          N += n;
+          if (lane == k) n_mine = n;
+          if (n < g.min_kw || n == 0) eligible = false;
+        }
+      }
+    };
     if (active) {
-      const uint32_t ty = a.metric_type ? a.metric_type[v] : 0u;
       tp = a.P->types[ty < a.P->n_types ? ty : 0u];
 
       // the rows of this warp's NEXT service into L2 while this one is computed: its first touches
       // would otherwise each wait for DRAM (a service is only ~7 KB)
-      const uint64_t vn = v + (uint64_t)gridDim.x * wpc;
-      if (vn < a.n_services) {
-        if (a.hist) {
-          const char* hp = reinterpret_cast<const char*>(a.hist + vn * a.hist_pitch);
-          for (uint32_t o = (uint32_t)lane * 128u; o < a.n_hist * 4u; o += 32u * 128u) fm_prefetch_l2(hp + o);
-        }
-        const uint32_t gn0 = a.group_offsets[vn], gn1 = a.group_offsets[vn + 1];
-        const uint32_t row_bytes = a.n_cur * 4u;
-        const uint32_t lines = (row_bytes + 127u) / 128u;           // per group row
-        for (uint32_t j = lane; j < (gn1 - gn0) * lines; j += 32u) {
-          const uint32_t k = j / lines, l = j - k * lines;
-          fm_prefetch_l2(reinterpret_cast<const char*>(a.cur + (uint64_t)(gn0 + k) * a.cur_pitch) + l * 128u);
-        }
+      if (more && a.hist) {
+        const char* hp = reinterpret_cast<const char*>(a.hist + vn * a.hist_pitch);
+        for (uint32_t o = (uint32_t)lane * 128u; o < a.n_hist * 4u; o += 32u * 128u) fm_prefetch_l2(hp + o);
       }
+      // this service's points: requested before the history stream, consumed after it
+      if (FM_GROUPS_EARLY && want_kw) load_points();
 
       // ---- a2: model from the pooled history (streamed from global memory) --------------------
       if (a.hist) {
         const uint32_t nh = row_len(a.hist_len, v, a.n_hist);
         model_ok = fm_model(g, a.hist + v * a.hist_pitch, nh, true, lane, mean, sigma);
+      }
+      if (more) {
+        const uint32_t row_bytes = a.n_cur * 4u;
+        const uint32_t lines = (row_bytes + 127u) / 128u;           // per group row
+        for (uint32_t j = lane; j < (ng1 - ng0) * lines; j += 32u) {
+          const uint32_t k = j / lines, l = j - k * lines;
+          fm_prefetch_l2(reinterpret_cast<const char*>(a.cur + (uint64_t)(ng0 + k) * a.cur_pitch) + l * 128u);
+        }
       }
     }
     if (kSyncTwice) __syncthreads();
@@ -243,23 +315,9 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
       if (differ) status_kw |= FM_ST_DIFFER;
     }
     if (want_kw) {
-      // groups into registers (neither path cares which key sits where)
-      float s[kR];
-      uint32_t N = 0, valid = 0, n_mine = 1;
-      bool eligible = K >= 2;
+      if (!FM_GROUPS_EARLY) load_points();
 #pragma unroll
-      for (int k = 0; k < kGroups; ++k) {
-        s[2 * k] = CUDART_INF_F; s[2 * k + 1] = CUDART_INF_F;
-        if ((uint32_t)k < K) {
-          const uint32_t n = row_len(a.cur_len, g0 + k, a.n_cur);
-          const float* row = a.cur + (uint64_t)(g0 + k) * a.cur_pitch;
-          if ((uint32_t)lane < n) { s[2 * k] = __ldg(row + lane) + 0.0f; valid |= 1u << (2 * k); }            // -0 -> +0
-          if ((uint32_t)lane + 32u < n) { s[2 * k + 1] = __ldg(row + lane + 32) + 0.0f; valid |= 2u << (2 * k); }
-          N += n;
-          if (lane == k) n_mine = n;
-          if (n < g.min_kw || n == 0) eligible = false;
-        }
-      }
+      for (int r = 0; r < kR; ++r) s[r] += 0.0f;  // -0 -> +0
       if (eligible) {
         uint32_t r2_mine = 0;                      // lane k: twice the rank sum of group k
         long long T = 0;
@@ -312,7 +370,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
     const float up_f = (tp.bound_mask & 1u) ? __double2float_rd(up) : CUDART_INF_F;
     const float lo_f = (tp.bound_mask & 2u) ? __double2float_ru(lo) : -CUDART_INF_F;
     uint32_t ba_mine = 0, bb_mine = 0, nc_mine = 0;     // lane k: flags and length of group k
-#pragma unroll 1
+#pragma unroll 2
     for (uint32_t k = 0; k < K; ++k) {
       const uint32_t nc = row_len(a.cur_len, g0 + k, a.n_cur);
       const float* row = a.cur + (uint64_t)(g0 + k) * a.cur_pitch;
@@ -360,11 +418,19 @@ __global__ void __launch_bounds__(kWarps * 32, 1) k_groups_sort(const FmGArgs a,
 
 }  // namespace
 
+void fm_groups_sort_shape(int* warps_per_cta, int* ctas_per_sm) { *warps_per_cta = kWarps; *ctas_per_sm = kCtas; }
+
 int fm_launch_groups_sort(const FmGArgs& a, uint32_t* defer_list, uint32_t* defer_n, int grid, cudaStream_t st) {
   constexpr int smem = kWarps * 32 * kR * 4;
   if (smem > 48 * 1024 &&
       cudaFuncSetAttribute(k_groups_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
     return 0;   // the caller's cudaGetLastError() reports it
-  k_groups_sort<<<grid, kWarps * 32, smem, st>>>(a, defer_list, defer_n);
+  // services between two CTA barriers (power of two); tuning switch, read once
+  static const uint32_t sync_every = [] {
+    const char* e = getenv("FOREMAST_CUDA_GROUPS_SYNC");
+    const long v = e ? atol(e) : (long)kSyncEvery;
+    return (v >= 1 && v <= 1024 && (v & (v - 1)) == 0) ? (uint32_t)v : kSyncEvery;
+  }();
+  k_groups_sort<<<grid, kWarps * 32, smem, st>>>(a, defer_list, defer_n, sync_every - 1u);
   return 1;
 }

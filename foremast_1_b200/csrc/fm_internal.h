@@ -62,6 +62,7 @@ int fm_launch_score(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t 
 int fm_launch_groups(const FmGArgs& a, int warps_per_cta, int grid, cudaStream_t st);
 // fm_groups.cu: services of <= 8 groups x <= 64 points; the others are appended to defer_list
 int fm_launch_groups_sort(const FmGArgs& a, uint32_t* defer_list, uint32_t* defer_n, int grid, cudaStream_t st);
+void fm_groups_sort_shape(int* warps_per_cta, int* ctas_per_sm);
 int fm_launch_canary_sort(const FmKArgs& a, int regs, int valid_regs, int warps_per_cta, int grid, cudaStream_t st);
 cudaError_t fm_canary_sort_smem_attr(int bytes);
 int fm_launch_canary_elect(const FmKArgs& a, int nv, int grid, cudaStream_t st);

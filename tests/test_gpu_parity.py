@@ -328,6 +328,48 @@ def test_groups_mixed_shapes(ctx, n_cur):
     assert (out["rec"]["status"] & A.FM_ST_KW_RUN).any()
 
 
+@pytest.mark.parametrize("distinct", [1, 2, 7, 31, 32, 33, 40, 64, 200])
+def test_groups_distinct_values(ctx, distinct):
+    """The rollover kernel ranks a pooled sample with at most 32 distinct values from a hash multiset and
+    anything else with the sorting network: both sides of that limit, values that collide in the table
+    (many services, arbitrary bit patterns), +-0, +-inf and denormals as values, ragged and empty groups."""
+    rng = np.random.default_rng(4000 + distinct)
+    V = 400
+    K = rng.integers(2, 9, V)
+    off = np.concatenate([[0], np.cumsum(K)]).astype(np.uint32)
+    G = int(off[-1])
+    cur = np.zeros((G, 64), np.float32)
+    for v in range(V):
+        kind = v % 4
+        if kind == 0:      # counts per second
+            vals = (np.arange(distinct) / 60.0).astype(np.float32)
+        elif kind == 1:    # arbitrary finite bit patterns
+            vals = rng.integers(0, 0x7F000000, distinct).astype(np.uint32).view(np.float32) * rng.choice([-1, 1], distinct).astype(np.float32)
+        elif kind == 2:    # specials among ordinary values
+            vals = rng.normal(0, 1, distinct).astype(np.float32)
+            sp = np.array([0.0, -0.0, np.inf, -np.inf, 1e-45, -1e-45, 3e-39], np.float32)
+            vals[:min(distinct, sp.size)] = sp[:min(distinct, sp.size)]
+        else:              # exactly `distinct` values, every one present
+            vals = rng.permutation(4096)[:distinct].astype(np.float32)
+        rows = slice(off[v], off[v + 1])
+        pick = rng.integers(0, distinct, (K[v], 64))
+        if kind == 3 and K[v] * 64 >= distinct:
+            pick.ravel()[:distinct] = np.arange(distinct)
+        cur[rows] = vals[pick]
+    cl = rng.integers(5, 65, G).astype(np.uint32)
+    cl[rng.random(G) < 0.6] = 64
+    cl[off[7]] = 0
+    hist = rng.normal(0.5, 0.2, (V, 300)).astype(np.float32)
+    mt = rng.integers(0, 6, V).astype(np.uint8)
+    g, t = params(pairwise_mode=A.FM_PW_KRUSKAL)
+    ctx.set_params(g, t)
+    out = ctx.score_groups(cur, off, hist, cur_len=cl, metric_type=mt)
+    ora = O.score_groups(g, t, out["batch"], n_threads=8)
+    assert_records_match(out["rec"], ora["rec"], cur, cl, bound_masks(t, np.repeat(mt, K), G))
+    assert (out["svc"] == ora["svc"]).all()
+    assert (out["rec"]["status"] & A.FM_ST_KW_RUN).any()
+
+
 @pytest.mark.parametrize("n_cur", [20, 60, 100])
 def test_groups_friedman(ctx, n_cur):
     """Friedman chi-square (docs/guides/design.md:92) on both rollover kernels: 3..16 groups, tied and
