@@ -95,6 +95,7 @@ struct fm_ctx {
   int count_warps = 0;             // FOREMAST_CUDA_WARPS: warps per SM of the counting kernel
   int ma_group = 0;                // FOREMAST_CUDA_MA_GROUP=4|8|16|32: lanes per series of k_ma_only
   int small_table = 0;             // FOREMAST_CUDA_SMALL_TABLE: elect path, load factor <= 0.8
+  int chunk_mb = 0;                // FOREMAST_CUDA_CHUNK_MB: rows per pipelined chunk of fm_score_groups (default 64 MB)
   std::string err;
 };
 
@@ -477,6 +478,7 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
   if (const char* e = getenv("FOREMAST_CUDA_WARPS")) { const int v = atoi(e); c->count_warps = (v >= 1 && v <= 32) ? v : 0; }
   if (const char* e = getenv("FOREMAST_CUDA_MA_GROUP")) { const int v = atoi(e); c->ma_group = (v == 2 || v == 4 || v == 8 || v == 16 || v == 32) ? v : 0; }
   c->small_table = getenv("FOREMAST_CUDA_SMALL_TABLE") != nullptr;
+  if (const char* e = getenv("FOREMAST_CUDA_CHUNK_MB")) { const int v = atoi(e); c->chunk_mb = (v >= 1 && v <= 4096) ? v : 0; }
   FM_CKC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   FM_CKC(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
   FM_CKC(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
@@ -1036,22 +1038,17 @@ static int32_t plan_groups(fm_ctx* c, const fm_group_batch* b, FmGArgs* a, int* 
   return FM_OK;
 }
 
-int32_t fm_score_groups_device(fm_ctx* c, const fm_group_batch* b, fm_series_rec* d_out,
-                               fm_rollup_rec* d_svc, fm_timing* timing) {
-  if (!c) return FM_E_INVALID;
-  if (!d_out) return fail(c, FM_E_INVALID, "null output");
-  FM_CK(c, cudaSetDevice(c->device));
-  if (timing) memset(timing, 0, sizeof(*timing));
+// Kernels of one device-resident group batch on the compute stream (no events, no wait).
+static int32_t groups_launch(fm_ctx* c, const fm_group_batch* b, fm_series_rec* d_out, fm_rollup_rec* d_svc,
+                             cudaEvent_t ev_main_done, uint32_t* launches) {
   FmGArgs a; int wpc = 1, grid = 1;
   int32_t rc = plan_groups(c, b, &a, &wpc, &grid);
   if (rc != FM_OK) return rc;
   if (b->n_services == 0) return FM_OK;
   a.out = d_out; a.svc = d_svc;
-  uint32_t launches = 0;
   if (d_svc) FM_CK(c, cudaMemsetAsync(d_svc, 0, b->n_services * sizeof(fm_rollup_rec), c->stream));
-  if (timing) FM_CK(c, cudaEventRecord(c->ev_a, c->stream));
   if (b->n_cur <= 64 && c->force_path != 1) {
-    // register-sort kernel for services of <= 8 groups; the rest (listed by it) go to the general one
+    // register kernel for services of <= 8 groups; the rest (listed by it) go to the general one
     const size_t al_n = (b->n_services * 4 + 255) & ~size_t(255);
     FM_CK(c, c->misc.reserve(al_n + 256));
     uint32_t* d_list = static_cast<uint32_t*>(c->misc.p);
@@ -1061,16 +1058,29 @@ int32_t fm_score_groups_device(fm_ctx* c, const fm_group_batch* b, fm_series_rec
     fm_groups_sort_shape(&gw, &gc);
     const uint64_t need = (b->n_services + gw - 1) / gw;
     const int g_fast = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * gc, need));
-    launches += fm_launch_groups_sort(a, d_list, d_cnt, g_fast, c->stream);
+    *launches += fm_launch_groups_sort(a, d_list, d_cnt, g_fast, c->stream);
     a.list = d_list; a.list_n = d_cnt;
-    launches += fm_launch_groups(a, wpc, std::min(grid, c->num_sms), c->stream);
+    *launches += fm_launch_groups(a, wpc, std::min(grid, c->num_sms), c->stream);
   } else {
-    launches += fm_launch_groups(a, wpc, grid, c->stream);
+    *launches += fm_launch_groups(a, wpc, grid, c->stream);
   }
-  if (timing) FM_CK(c, cudaEventRecord(c->ev_m, c->stream));
-  launches += fm_launch_rollup_finalize_one(d_svc, b->n_services, c->stream);
+  if (ev_main_done) FM_CK(c, cudaEventRecord(ev_main_done, c->stream));
+  *launches += fm_launch_rollup_finalize_one(d_svc, b->n_services, c->stream);
   FM_CK(c, cudaGetLastError());
-  if (timing) {
+  return FM_OK;
+}
+
+int32_t fm_score_groups_device(fm_ctx* c, const fm_group_batch* b, fm_series_rec* d_out,
+                               fm_rollup_rec* d_svc, fm_timing* timing) {
+  if (!c) return FM_E_INVALID;
+  if (!d_out) return fail(c, FM_E_INVALID, "null output");
+  FM_CK(c, cudaSetDevice(c->device));
+  if (timing) memset(timing, 0, sizeof(*timing));
+  uint32_t launches = 0;
+  if (timing) FM_CK(c, cudaEventRecord(c->ev_a, c->stream));
+  int32_t rc = groups_launch(c, b, d_out, d_svc, timing ? c->ev_m : nullptr, &launches);
+  if (rc != FM_OK) return rc;
+  if (timing && b->n_services) {
     FM_CK(c, cudaEventRecord(c->ev_b, c->stream));
     FM_CK(c, cudaEventSynchronize(c->ev_b));
     FM_CK(c, cudaEventElapsedTime(&timing->kernel_ms, c->ev_a, c->ev_b));
@@ -1080,12 +1090,16 @@ int32_t fm_score_groups_device(fm_ctx* c, const fm_group_batch* b, fm_series_rec
   return FM_OK;
 }
 
+// Host rows: the batch is cut at service boundaries into chunks of ~64 MB of rows; the upload of
+// chunk i+1 (copy stream) runs beside the kernels of chunk i (compute stream) and the read-back of
+// chunk i-1 (second copy stream), two buffer slots as in fm_score_batch.
 int32_t fm_score_groups(fm_ctx* c, const fm_group_batch* b, fm_series_rec* out, fm_rollup_rec* out_svc,
                         fm_timing* timing) {
   if (!c) return FM_E_INVALID;
   if (!b || !out) return fail(c, FM_E_INVALID, "null batch or output");
   if (b->struct_size != sizeof(fm_group_batch)) return fail(c, FM_E_INVALID, "bad fm_group_batch.struct_size");
   FM_CK(c, cudaSetDevice(c->device));
+  if (timing) memset(timing, 0, sizeof(*timing));
   auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
   const uint64_t V = b->n_services, G = b->n_groups;
   // the kernels index the output by these offsets: they must walk [0, n_groups] without a step back
@@ -1095,47 +1109,117 @@ int32_t fm_score_groups(fm_ctx* c, const fm_group_batch* b, fm_series_rec* out, 
     if (b->group_offsets[v + 1] < b->group_offsets[v]) return fail(c, FM_E_INVALID, "group_offsets must be non-decreasing (service %llu)", (unsigned long long)v);
     if (b->group_offsets[v + 1] - b->group_offsets[v] > FM_MAX_GROUPS) return fail(c, FM_E_UNSUPPORTED, "service %llu has more than %u groups", (unsigned long long)v, FM_MAX_GROUPS);
   }
+  if (G && !b->cur) return fail(c, FM_E_INVALID, "null cur");
+  if (V == 0) return FM_OK;
+
+  // chunks: [first service, first group) of each, offsets rebased to the chunk
+  const size_t svc_bytes = b->hist ? (size_t)b->hist_pitch * 4 : 0, grp_bytes = (size_t)b->cur_pitch * 4;
+  const size_t target = size_t(c->chunk_mb ? c->chunk_mb : 64) << 20;
+  std::vector<uint64_t> cut_v(1, 0);
+  {
+    size_t acc = 0;
+    for (uint64_t v = 0; v < V; ++v) {
+      acc += svc_bytes + grp_bytes * (b->group_offsets[v + 1] - b->group_offsets[v]);
+      if (acc >= target && v + 1 < V) { cut_v.push_back(v + 1); acc = 0; }
+    }
+    cut_v.push_back(V);
+  }
+  const uint64_t n_chunks = cut_v.size() - 1;
+  uint64_t max_v = 0, max_g = 0;
+  std::vector<uint32_t> reb(V + n_chunks);                 // chunk ci: reb[cut_v[ci] + ci ..], V_c + 1 entries
+  for (uint64_t ci = 0; ci < n_chunks; ++ci) {
+    const uint64_t v0 = cut_v[ci], v1 = cut_v[ci + 1];
+    const uint32_t g0 = b->group_offsets[v0];
+    for (uint64_t v = v0; v <= v1; ++v) reb[v + ci] = b->group_offsets[v] - g0;
+    max_v = std::max(max_v, v1 - v0);
+    max_g = std::max<uint64_t>(max_g, b->group_offsets[v1] - g0);
+  }
   size_t o = 0;
-  const size_t o_off = o;  o += al((V + 1) * 4);
-  const size_t o_cur = o;  o += al(G * b->cur_pitch * 4);
-  const size_t o_clen = o; o += b->cur_len ? al(G * 4) : 0;
-  const size_t o_hist = o; o += b->hist ? al(V * b->hist_pitch * 4) : 0;
-  const size_t o_hlen = o; o += (b->hist && b->hist_len) ? al(V * 4) : 0;
-  const size_t o_mt = o;   o += b->metric_type ? al(V) : 0;
-  FM_CK(c, c->in[0].reserve(o));
-  const size_t o_svc = al(G * sizeof(fm_series_rec));
-  FM_CK(c, c->out[0].reserve(o_svc + al(V * sizeof(fm_rollup_rec))));
-  char* din = static_cast<char*>(c->in[0].p);
-  char* dout = static_cast<char*>(c->out[0].p);
-  uint64_t h2d = 0;
-  auto up = [&](size_t off, const void* src, size_t bytes) -> cudaError_t {
-    h2d += bytes;
-    return cudaMemcpyAsync(din + off, src, bytes, cudaMemcpyHostToDevice, c->stream);
-  };
-  FM_CK(c, up(o_off, b->group_offsets, (V + 1) * 4));
-  if (G) FM_CK(c, up(o_cur, b->cur, G * b->cur_pitch * 4));
-  if (b->cur_len && G) FM_CK(c, up(o_clen, b->cur_len, G * 4));
-  if (b->hist && V) FM_CK(c, up(o_hist, b->hist, V * b->hist_pitch * 4));
-  if (b->hist && b->hist_len && V) FM_CK(c, up(o_hlen, b->hist_len, V * 4));
-  if (b->metric_type && V) FM_CK(c, up(o_mt, b->metric_type, V));
-  fm_group_batch db = *b;
-  db.group_offsets = reinterpret_cast<const uint32_t*>(din + o_off);
-  db.cur = reinterpret_cast<const float*>(din + o_cur);
-  db.cur_len = b->cur_len ? reinterpret_cast<const uint32_t*>(din + o_clen) : nullptr;
-  db.hist = b->hist ? reinterpret_cast<const float*>(din + o_hist) : nullptr;
-  db.hist_len = (b->hist && b->hist_len) ? reinterpret_cast<const uint32_t*>(din + o_hlen) : nullptr;
-  db.metric_type = b->metric_type ? reinterpret_cast<const uint8_t*>(din + o_mt) : nullptr;
-  fm_timing t; memset(&t, 0, sizeof(t));
-  int32_t rc = fm_score_groups_device(c, &db, reinterpret_cast<fm_series_rec*>(dout),
-                                      out_svc ? reinterpret_cast<fm_rollup_rec*>(dout + o_svc) : nullptr, &t);
-  if (rc != FM_OK) return rc;
-  if (G) FM_CK(c, cudaMemcpyAsync(out, dout, G * sizeof(fm_series_rec), cudaMemcpyDeviceToHost, c->stream));
-  if (out_svc && V) FM_CK(c, cudaMemcpyAsync(out_svc, dout + o_svc, V * sizeof(fm_rollup_rec), cudaMemcpyDeviceToHost, c->stream));
-  FM_CK(c, cudaStreamSynchronize(c->stream));
+  const size_t o_off = o;  o += al((max_v + 1) * 4);
+  const size_t o_cur = o;  o += al(max_g * b->cur_pitch * 4);
+  const size_t o_clen = o; o += b->cur_len ? al(max_g * 4) : 0;
+  const size_t o_hist = o; o += b->hist ? al(max_v * b->hist_pitch * 4) : 0;
+  const size_t o_hlen = o; o += (b->hist && b->hist_len) ? al(max_v * 4) : 0;
+  const size_t o_mt = o;   o += b->metric_type ? al(max_v) : 0;
+  const size_t in_bytes = o;
+  const size_t o_svc = al(max_g * sizeof(fm_series_rec));
+  const size_t out_bytes = o_svc + al(max_v * sizeof(fm_rollup_rec));
+  const int slots = n_chunks > 1 ? 2 : 1;
+  for (int i = 0; i < slots; ++i) { FM_CK(c, c->in[i].reserve(in_bytes)); FM_CK(c, c->out[i].reserve(out_bytes)); }
+  while (c->kev.size() < 2 * n_chunks) {
+    cudaEvent_t e; FM_CK(c, cudaEventCreate(&e)); c->kev.push_back(e);
+  }
+  uint32_t launches = 0;
+  uint64_t h2d = 0, d2h = 0;
+  auto drain = [&]() { cudaStreamSynchronize(c->s_h2d); cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->s_d2h); };
+#define FM_CKL(call)                                                                  \
+  do {                                                                                \
+    cudaError_t e__ = (call);                                                         \
+    if (e__ != cudaSuccess) {                                                         \
+      drain();                                                                        \
+      return fail(c, e__ == cudaErrorMemoryAllocation ? FM_E_NOMEM : FM_E_CUDA,       \
+                  "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__,  \
+                  __LINE__);                                                          \
+    }                                                                                 \
+  } while (0)
+  for (uint64_t ci = 0; ci < n_chunks; ++ci) {
+    const int s = (int)(ci & 1);
+    const uint64_t v0 = cut_v[ci], nv = cut_v[ci + 1] - v0;
+    const uint64_t g0 = b->group_offsets[v0], ng = b->group_offsets[v0 + nv] - g0;
+    char* din = static_cast<char*>(c->in[s].p);
+    char* dout = static_cast<char*>(c->out[s].p);
+    if (ci >= 2) FM_CKL(cudaStreamWaitEvent(c->s_h2d, c->in_free[s], 0));
+    auto up = [&](size_t off, const void* src, size_t bytes) -> cudaError_t {
+      h2d += bytes;
+      return cudaMemcpyAsync(din + off, src, bytes, cudaMemcpyHostToDevice, c->s_h2d);
+    };
+    FM_CKL(up(o_off, reb.data() + v0 + ci, (nv + 1) * 4));
+    if (ng) FM_CKL(up(o_cur, b->cur + g0 * b->cur_pitch, ng * b->cur_pitch * 4));
+    if (b->cur_len && ng) FM_CKL(up(o_clen, b->cur_len + g0, ng * 4));
+    if (b->hist) FM_CKL(up(o_hist, b->hist + v0 * b->hist_pitch, nv * b->hist_pitch * 4));
+    if (b->hist && b->hist_len) FM_CKL(up(o_hlen, b->hist_len + v0, nv * 4));
+    if (b->metric_type) FM_CKL(up(o_mt, b->metric_type + v0, nv));
+    FM_CKL(cudaEventRecord(c->in_ready[s], c->s_h2d));
+
+    fm_group_batch db = *b;
+    db.n_services = nv; db.n_groups = ng;
+    db.group_offsets = reinterpret_cast<const uint32_t*>(din + o_off);
+    db.cur = reinterpret_cast<const float*>(din + o_cur);
+    db.cur_len = b->cur_len ? reinterpret_cast<const uint32_t*>(din + o_clen) : nullptr;
+    db.hist = b->hist ? reinterpret_cast<const float*>(din + o_hist) : nullptr;
+    db.hist_len = (b->hist && b->hist_len) ? reinterpret_cast<const uint32_t*>(din + o_hlen) : nullptr;
+    db.metric_type = b->metric_type ? reinterpret_cast<const uint8_t*>(din + o_mt) : nullptr;
+    FM_CKL(cudaStreamWaitEvent(c->stream, c->in_ready[s], 0));
+    if (ci >= 2) FM_CKL(cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
+    FM_CKL(cudaEventRecord(c->kev[2 * ci], c->stream));
+    const int32_t rc = groups_launch(c, &db, reinterpret_cast<fm_series_rec*>(dout),
+                                     out_svc ? reinterpret_cast<fm_rollup_rec*>(dout + o_svc) : nullptr, nullptr, &launches);
+    if (rc != FM_OK) { drain(); return rc; }
+    FM_CKL(cudaEventRecord(c->kev[2 * ci + 1], c->stream));
+    FM_CKL(cudaEventRecord(c->in_free[s], c->stream));
+    FM_CKL(cudaEventRecord(c->out_ready[s], c->stream));
+
+    FM_CKL(cudaStreamWaitEvent(c->s_d2h, c->out_ready[s], 0));
+    if (ng) FM_CKL(cudaMemcpyAsync(out + g0, dout, ng * sizeof(fm_series_rec), cudaMemcpyDeviceToHost, c->s_d2h));
+    d2h += ng * sizeof(fm_series_rec);
+    if (out_svc) {
+      FM_CKL(cudaMemcpyAsync(out_svc + v0, dout + o_svc, nv * sizeof(fm_rollup_rec), cudaMemcpyDeviceToHost, c->s_d2h));
+      d2h += nv * sizeof(fm_rollup_rec);
+    }
+    FM_CKL(cudaEventRecord(c->out_free[s], c->s_d2h));
+  }
+#undef FM_CKL
+  cudaError_t e1 = cudaStreamSynchronize(c->s_h2d), e2 = cudaStreamSynchronize(c->stream), e3 = cudaStreamSynchronize(c->s_d2h);
+  FM_CK(c, e1); FM_CK(c, e2); FM_CK(c, e3);
   if (timing) {
-    *timing = t;
-    timing->h2d_bytes = h2d;
-    timing->d2h_bytes = G * sizeof(fm_series_rec) + (out_svc ? V * sizeof(fm_rollup_rec) : 0);
+    float tot = 0.f;
+    for (uint64_t ci = 0; ci < n_chunks; ++ci) {
+      float ms = 0.f;
+      FM_CK(c, cudaEventElapsedTime(&ms, c->kev[2 * ci], c->kev[2 * ci + 1]));
+      tot += ms;
+    }
+    timing->kernel_ms = tot; timing->main_kernel_ms = tot; timing->launches = launches;
+    timing->h2d_bytes = h2d; timing->d2h_bytes = d2h;
   }
   return FM_OK;
 }

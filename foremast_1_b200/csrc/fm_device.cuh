@@ -473,21 +473,27 @@ __device__ __forceinline__ FmTest fm_wilcoxon(long long w2p, long long w2m, long
   return t;
 }
 
+// 1/j for the chi-square series (entry 0 unused)
+static __constant__ double fm_inv_small[32] = {
+    0.0, 1.0, 1.0 / 2, 1.0 / 3, 1.0 / 4, 1.0 / 5, 1.0 / 6, 1.0 / 7, 1.0 / 8, 1.0 / 9, 1.0 / 10, 1.0 / 11, 1.0 / 12, 1.0 / 13,
+    1.0 / 14, 1.0 / 15, 1.0 / 16, 1.0 / 17, 1.0 / 18, 1.0 / 19, 1.0 / 20, 1.0 / 21, 1.0 / 22, 1.0 / 23, 1.0 / 24, 1.0 / 25,
+    1.0 / 26, 1.0 / 27, 1.0 / 28, 1.0 / 29, 1.0 / 30, 1.0 / 31};
 // A.5 chi-square survival, integer dof, closed form
 __device__ __forceinline__ double fm_chi2_sf(double x, uint32_t dof) {
   if (!(x > 0.0) || dof == 0) return 1.0;
   const double hx = 0.5 * x;
   const double e = exp(-hx);
   const uint32_t m = dof >> 1;
+  // (terms by a table of reciprocals: an fp64 division is ~30 instructions; dof <= FM_MAX_GROUPS - 1 = 15)
   if ((dof & 1u) == 0u) {
     double term = 1.0, sum = 1.0;
-    for (uint32_t j = 1; j < m; ++j) { term *= hx / (double)j; sum += term; }
+    for (uint32_t j = 1; j < m; ++j) { term *= hx * fm_inv_small[j & 31u]; sum += term; }
     return e * sum;
   }
   double q = erfc(sqrt(hx));
   if (m > 0) {
     double term = 1.0, sum = 1.0;
-    for (uint32_t j = 2; j <= m; ++j) { term *= x / (double)(2 * j - 1); sum += term; }
+    for (uint32_t j = 2; j <= m; ++j) { term *= x * fm_inv_small[(2 * j - 1) & 31u]; sum += term; }
     q += e * sqrt(2.0 * x / 3.14159265358979323846) * sum;
   }
   return q;

@@ -328,6 +328,39 @@ def test_groups_mixed_shapes(ctx, n_cur):
     assert (out["rec"]["status"] & A.FM_ST_KW_RUN).any()
 
 
+def test_groups_multi_chunk_pipeline(monkeypatch):
+    """fm_score_groups cuts a batch at service boundaries into chunks that are uploaded, scored and
+    read back on three streams: with 1 MB chunks a 3000-service batch takes ~20 of them, both buffer
+    slots are reused, and the records equal the one-chunk result byte for byte."""
+    rng = np.random.default_rng(77)
+    V = 3000
+    K = rng.integers(1, 13, V)                      # > 8 groups: deferred list inside a chunk
+    off = np.concatenate([[0], np.cumsum(K)]).astype(np.uint32)
+    G = int(off[-1])
+    cur = rng.poisson(3.0, (G, 60)).astype(np.float32) / np.float32(60)
+    cur[rng.random(G) < 0.3] = rng.normal(5, 1, 60).astype(np.float32)
+    hist = rng.normal(0.05, 0.03, (V, 1440)).astype(np.float32)
+    cl = rng.integers(0, 61, G).astype(np.uint32)
+    cl[rng.random(G) < 0.8] = 60
+    hl = np.full(V, 1440, np.uint32); hl[::17] = 5
+    mt = rng.integers(0, 6, V).astype(np.uint8)
+    g, t = params(pairwise_mode=A.FM_PW_KRUSKAL)
+    with Context(0) as one:
+        one.set_params(g, t)
+        ref = one.score_groups(cur, off, hist, cur_len=cl, hist_len=hl, metric_type=mt)
+    monkeypatch.setenv("FOREMAST_CUDA_CHUNK_MB", "1")
+    with Context(0) as many:
+        many.set_params(g, t)
+        out = many.score_groups(cur, off, hist, cur_len=cl, hist_len=hl, metric_type=mt)
+        again = many.score_groups(cur, off, hist, cur_len=cl, hist_len=hl, metric_type=mt)
+    assert out["timing"].launches > 3 * ref["timing"].launches
+    assert out["rec"].tobytes() == ref["rec"].tobytes() and out["svc"].tobytes() == ref["svc"].tobytes()
+    assert again["rec"].tobytes() == ref["rec"].tobytes() and again["svc"].tobytes() == ref["svc"].tobytes()
+    ora = O.score_groups(g, t, ref["batch"], n_threads=8)
+    assert_records_match(ref["rec"], ora["rec"], cur, cl, bound_masks(t, np.repeat(mt, K), G))
+    assert (ref["svc"] == ora["svc"]).all()
+
+
 @pytest.mark.parametrize("distinct", [1, 2, 7, 31, 32, 33, 40, 64, 200])
 def test_groups_distinct_values(ctx, distinct):
     """The rollover kernel ranks a pooled sample with at most 32 distinct values from a hash multiset and
