@@ -58,6 +58,9 @@ struct RowCache {
   uint32_t epoch = 0;
   std::vector<uint64_t> prev_ids;           // ids and slots of the previous call: a re-poll of the
   std::vector<uint32_t> prev_slot;          // same job set resolves without a single hash lookup
+  std::vector<uint8_t> miss;                // per row of the current call: has to be uploaded
+  bool prev_clean = false;                  // every row of the previous call was resident when it ended
+  bool any_miss = false;
   uint64_t hits = 0, misses = 0, evictions = 0, uncached = 0;
 
   void release() {
@@ -66,7 +69,7 @@ struct RowCache {
     d_base = d_hist = nullptr;
     cap = 0; n_live = 0; hand = 0;
     slot_id.clear(); slot_epoch.clear(); slot_blen.clear(); slot_hlen.clear(); slot_live.clear();
-    index.clear(); prev_ids.clear(); prev_slot.clear();
+    index.clear(); prev_ids.clear(); prev_slot.clear(); miss.clear(); prev_clean = false;
   }
 };
 
@@ -95,6 +98,7 @@ struct fm_ctx {
   int count_warps = 0;             // FOREMAST_CUDA_WARPS: warps per SM of the counting kernel
   int ma_group = 0;                // FOREMAST_CUDA_MA_GROUP=4|8|16|32: lanes per series of k_ma_only
   int small_table = 0;             // FOREMAST_CUDA_SMALL_TABLE: elect path, load factor <= 0.8
+  int force_gather = 0;            // FOREMAST_CUDA_GATHER: cached rows are copied into the chunk even for kernels that read the cache in place
   int chunk_mb = 0;                // FOREMAST_CUDA_CHUNK_MB: rows per pipelined chunk of fm_score_groups (default 64 MB)
   std::string err;
 };
@@ -478,6 +482,7 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
   if (const char* e = getenv("FOREMAST_CUDA_WARPS")) { const int v = atoi(e); c->count_warps = (v >= 1 && v <= 32) ? v : 0; }
   if (const char* e = getenv("FOREMAST_CUDA_MA_GROUP")) { const int v = atoi(e); c->ma_group = (v == 2 || v == 4 || v == 8 || v == 16 || v == 32) ? v : 0; }
   c->small_table = getenv("FOREMAST_CUDA_SMALL_TABLE") != nullptr;
+  c->force_gather = getenv("FOREMAST_CUDA_GATHER") != nullptr;
   if (const char* e = getenv("FOREMAST_CUDA_CHUNK_MB")) { const int v = atoi(e); c->chunk_mb = (v >= 1 && v <= 4096) ? v : 0; }
   FM_CKC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   FM_CKC(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
@@ -667,22 +672,34 @@ int32_t cache_prepare(fm_ctx* c, const fm_batch* b, bool canary, RowCache** on) 
   return FM_OK;
 }
 
-// Slot of every row of the call (kNone: the cache is full of rows of this very call -> that row
-// is uploaded into the chunk buffer like an uncached one) and whether it has to be uploaded.
-void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t S, bool canary,
-                  std::vector<uint32_t>& slot, std::vector<uint8_t>& miss) {
-  slot.resize(S); miss.assign(S, 0);
+// Slot of every row of the call, left in k.prev_slot (kNone: the cache is full of rows of this very
+// call -> that row is uploaded into the chunk buffer like an uncached one), and k.miss: whether the
+// row has to be uploaded.  A re-poll of exactly the previous call's rows (the steady state of the
+// job loop) costs one memcmp and one pass that stamps the slots as used.
+void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t S, bool canary) {
+  std::vector<uint32_t>& slot = k.prev_slot;
+  std::vector<uint8_t>& miss = k.miss;
   if (++k.epoch == 0) {                                   // epoch wrapped: nobody is "in use"
     std::fill(k.slot_epoch.begin(), k.slot_epoch.end(), 0u);
     k.epoch = 1;
   }
+  const uint64_t prev_n = k.prev_ids.size();
+  if (k.prev_clean && prev_n == S && memcmp(ids, k.prev_ids.data(), S * sizeof(uint64_t)) == 0) {
+    for (uint64_t s = 0; s < S; ++s) k.slot_epoch[slot[s]] = k.epoch;
+    k.hits += S;
+    if (k.any_miss || miss.size() != S) miss.assign(S, 0);
+    k.any_miss = false;
+    return;
+  }
+  if (slot.size() < S) slot.resize(S);
+  miss.assign(S, 0);
+  k.any_miss = false;
   // pass 1: rows that are resident (and protect their slots from this call's evictions)
-  const bool have_prev = !k.prev_ids.empty();
   for (uint64_t s = 0; s < S; ++s) {
     const uint64_t id = ids[s];
     uint32_t sl = RowCache::kNone;
-    if (have_prev && s < k.prev_ids.size() && k.prev_ids[s] == id) {
-      const uint32_t ps = k.prev_slot[s];
+    if (s < prev_n && k.prev_ids[s] == id) {
+      const uint32_t ps = slot[s];
       if (ps != RowCache::kNone && k.slot_live[ps] && k.slot_id[ps] == id) sl = ps;
     }
     if (sl == RowCache::kNone) {
@@ -694,6 +711,7 @@ void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t 
   }
   // pass 2: a slot for every other row: a free one, else the least recently scored one that this
   // call does not use (clock hand, 64 candidates); none left -> the row stays uncached
+  bool clean = true;
   for (uint64_t s = 0; s < S; ++s) {
     if (slot[s] != RowCache::kNone) continue;
     const uint64_t id = ids[s];
@@ -723,6 +741,7 @@ void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t 
       }
     }
     miss[s] = 1;
+    k.any_miss = true;
     if (sl != RowCache::kNone) {
       k.slot_live[sl] = 1; ++k.n_live;
       k.slot_id[sl] = id;
@@ -733,11 +752,13 @@ void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t 
       ++k.misses;
     } else {
       ++k.uncached;
+      clean = false;
     }
     slot[s] = sl;
   }
+  slot.resize(S);
   k.prev_ids.assign(ids, ids + S);
-  k.prev_slot = slot;
+  k.prev_clean = clean;
 }
 
 int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, void* out, fm_rank_aux* out_aux,
@@ -755,8 +776,6 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
 
   // row cache: slot per row, which rows still have to come over PCIe
   RowCache* kcp = nullptr;
-  std::vector<uint32_t> slot;
-  std::vector<uint8_t> miss;
   std::vector<uint32_t> eff_blen, eff_hlen;
   if (row_ids) {
     rc = cache_prepare(c, b, canary, &kcp);
@@ -764,8 +783,10 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
   }
   const bool cached = kcp != nullptr;
   RowCache& kc = cached ? *kcp : c->cache[0];
+  const std::vector<uint32_t>& slot = kc.prev_slot;
+  const std::vector<uint8_t>& miss = kc.miss;
   if (cached) {
-    cache_assign(kc, b, row_ids, S, canary, slot, miss);
+    cache_assign(kc, b, row_ids, S, canary);
     // lengths: a resident row keeps the length it was stored with
     if (canary && b->base_len) {
       eff_blen.resize(S);
@@ -857,7 +878,7 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
       // rows the cache does not hold yet: one copy per run of consecutive rows whose slots are
       // consecutive too (a cold cache hands out consecutive slots, so runs are long); rows that
       // found no slot go straight into the chunk buffer
-      uint64_t i = 0;
+      uint64_t i = kc.any_miss ? 0 : n;
       while (i < n) {
         if (!miss[s0 + i]) { ++i; continue; }
         const uint32_t sl0 = slot[s0 + i];
@@ -906,10 +927,15 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
     FM_CKL(cudaStreamWaitEvent(c->stream, c->in_ready[s], 0));
     if (ci >= 2) FM_CKL(cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
     FM_CKL(cudaEventRecord(c->kev[2 * ci], c->stream));
-    if (cached) {   // resident rows -> the chunk's row matrices (HBM to HBM)
+    if (cached) {
       const uint32_t* d_slot = reinterpret_cast<const uint32_t*>(din + o_slot);
-      if (canary) launches += fm_launch_gather_rows(kc.d_base, b->base_pitch, d_slot, reinterpret_cast<float*>(din + o_base), n, c->stream);
-      if (b->hist) launches += fm_launch_gather_rows(kc.d_hist, b->hist_pitch, d_slot, reinterpret_cast<float*>(din + o_hist), n, c->stream);
+      if ((pl.kind == 4 || pl.kind == 5 || pl.kind == 6) && !c->force_gather) {
+        // these kernels read resident rows in place (fm_base_row / fm_hist_row)
+        pl.a.row_slot = d_slot; pl.a.cache_base = kc.d_base; pl.a.cache_hist = kc.d_hist;
+      } else {   // resident rows -> the chunk's row matrices (HBM to HBM)
+        if (canary) launches += fm_launch_gather_rows(kc.d_base, b->base_pitch, d_slot, reinterpret_cast<float*>(din + o_base), n, c->stream);
+        if (b->hist) launches += fm_launch_gather_rows(kc.d_hist, b->hist_pitch, d_slot, reinterpret_cast<float*>(din + o_hist), n, c->stream);
+      }
     }
     launches += launch_plan(pl, c->stream);
     FM_CKL(cudaGetLastError());

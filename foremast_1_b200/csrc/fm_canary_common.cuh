@@ -24,7 +24,7 @@ __device__ __forceinline__ void issue_rows(const FmKArgs& a, float* stage, uint6
   const uint32_t cb = ((nc + 3u) & ~3u) * 4u, bb = ((nb + 3u) & ~3u) * 4u;
   fm_mbar_expect_tx(bar, cb + bb);
   if (cb) fm_bulk_g2s(stage, a.cur + s * a.cur_pitch, cb, bar);
-  if (bb) fm_bulk_g2s(stage + kCur, a.base + s * a.base_pitch, bb, bar);
+  if (bb) fm_bulk_g2s(stage + kCur, fm_base_row(a, s), bb, bar);
 }
 
 // ---- 64 keys across the warp (a = index lane, b = index lane + 32), ascending -------------

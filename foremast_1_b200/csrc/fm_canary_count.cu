@@ -385,7 +385,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
     const uint64_t sn = s + stride;
     if (sn < a.n_series) {     // pull the next rows into L2 while this series is ranked
       const uint32_t nbn = row_len(a.base_len, sn, a.n_base);
-      const char* pb = reinterpret_cast<const char*>(a.base + sn * a.base_pitch);
+      const char* pb = reinterpret_cast<const char*>(fm_base_row(a, sn));
       for (uint32_t o = (uint32_t)lane * 128u; o < nbn * 4u; o += 4096u) fm_prefetch_l2(pb + o);
       if (lane < 2) fm_prefetch_l2(reinterpret_cast<const char*>(a.cur + sn * a.cur_pitch) + lane * 128);
     }
@@ -487,7 +487,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
       }
     }
     if (a.hist) {
-      const ModelOut mo = model_call(&g, a.hist + s * a.hist_pitch, row_len(a.hist_len, s, a.n_hist), true, lane);
+      const ModelOut mo = model_call(&g, fm_hist_row(a, s), row_len(a.hist_len, s, a.n_hist), true, lane);
       model_ok = mo.ok; rec.mean = mo.mean; rec.sigma = mo.sigma;
     } else if (fuse_model)
       model_ok = nb >= max(g.min_hist_points, g.ddof + 1u);
@@ -668,7 +668,7 @@ __device__ __forceinline__ void issue_rows_pair(const FmKArgs& a, float* stage, 
   const uint32_t cb = ((nc + 3u) & ~3u) * 4u, bb = ((nb + 3u) & ~3u) * 4u;
   fm_mbar_expect_tx(bar, cb + bb);
   if (cb) fm_bulk_g2s(stage, a.cur + s * a.cur_pitch, cb, bar);
-  if (bb) fm_bulk_g2s(stage + kPairCurPad, a.base + s * a.base_pitch, bb, bar);
+  if (bb) fm_bulk_g2s(stage + kPairCurPad, fm_base_row(a, s), bb, bar);
 }
 
 __global__ void __launch_bounds__(512, 1) k_canary_team(const FmKArgs a) {
@@ -706,7 +706,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_team(const FmKArgs a) {
     const uint64_t sn = s + gridDim.x;
     if (sn < a.n_series) {     // pull the next rows into L2 while this series is ranked
       const uint32_t nbn = row_len(a.base_len, sn, a.n_base);
-      const char* pb = reinterpret_cast<const char*>(a.base + sn * a.base_pitch);
+      const char* pb = reinterpret_cast<const char*>(fm_base_row(a, sn));
       for (uint32_t o = threadIdx.x * 128u; o < nbn * 4u; o += blockDim.x * 128u) fm_prefetch_l2(pb + o);
       if (threadIdx.x < 2) fm_prefetch_l2(reinterpret_cast<const char*>(a.cur + sn * a.cur_pitch) + threadIdx.x * 128);
     }
@@ -751,7 +751,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_team(const FmKArgs a) {
       }
     } else if (w1) {
       if (want_wx) wx = wilcoxon_ints(g, wilcoxon_load(g, stage_s, nc, nb, lane, kPairCurPad), lane);
-      if (a.hist) mo = model_call(&g, a.hist + s * a.hist_pitch, row_len(a.hist_len, s, a.n_hist), true, lane);
+      if (a.hist) mo = model_call(&g, fm_hist_row(a, s), row_len(a.hist_len, s, a.n_hist), true, lane);
       else if (!fuse_model) mo = model_call(&g, stage + kPairCurPad, nb, false, lane);
     }
 

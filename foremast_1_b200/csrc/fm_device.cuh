@@ -169,6 +169,22 @@ __device__ __forceinline__ long long fm_tie(uint32_t t) {
 }
 
 // ------------------------------------------------------------- moments -----
+// Baseline / history row of series s: in the caller's matrix, or in place in the row cache.
+__device__ __forceinline__ const float* fm_base_row(const FmKArgs& a, uint64_t s) {
+  if (a.row_slot) {
+    const uint32_t sl = __ldg(a.row_slot + s);
+    if (sl != 0xFFFFFFFFu) return a.cache_base + (uint64_t)sl * a.base_pitch;
+  }
+  return a.base + s * a.base_pitch;
+}
+__device__ __forceinline__ const float* fm_hist_row(const FmKArgs& a, uint64_t s) {
+  if (a.row_slot) {
+    const uint32_t sl = __ldg(a.row_slot + s);
+    if (sl != 0xFFFFFFFFu) return a.cache_hist + (uint64_t)sl * a.hist_pitch;
+  }
+  return a.hist + s * a.hist_pitch;
+}
+
 // A.1: mean / sigma of a window with a pivot (the first sample) subtracted
 // before squaring so that sum(d^2) - sum(d)^2/n does not cancel
 // (SURVEY.md 7.2-4).  Partial sums are per lane; fm_moments_finish reduces.

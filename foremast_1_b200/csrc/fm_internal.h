@@ -39,6 +39,12 @@ struct FmKArgs {
   uint32_t log_m;          // k_canary_elect: log2 of the election table size; k_canary_count: its slot count
   uint32_t cnt_nv, cnt_ns; // k_canary_count: vector rows / scalar rows of the staged baseline per lane
   double* hw_scratch;      // k_score_series, Holt-Winters: season_len doubles per resident warp
+  // rows resident in the ctx's row cache (fm_score_batch_cached), read in place by k_canary_count,
+  // k_canary_team and k_ma_only: series s takes its baseline / history row from slot row_slot[s] of
+  // the cache unless that is 0xFFFFFFFF (row not resident: it is in base / hist like any other)
+  const uint32_t* row_slot;
+  const float* cache_base;
+  const float* cache_hist;
 };
 
 struct FmGArgs {

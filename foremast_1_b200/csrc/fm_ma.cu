@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs
     const bool live = s < a.n_series;
     const uint32_t nh = live ? row_len(a.hist_len, s, a.n_hist) : 0u;
     const uint32_t nc = live ? row_len(a.cur_len, s, a.n_cur) : 0u;
-    const float* hx = a.hist + (live ? s : 0) * a.hist_pitch;
+    const float* hx = fm_hist_row(a, live ? s : 0);
     const float4* h4 = reinterpret_cast<const float4*>(hx);
 
     // current row: requested before the history so that its latency hides under the moments
