@@ -85,18 +85,24 @@ __global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs
     // shorter than one vector fetch it on their own)
     const float p0 = __shfl_sync(FM_FULL, q[0].x, lane & ~(G - 1));
     const double pivot = nh >= 4u ? (double)p0 : (nh ? (double)__ldg(hx) : 0.0);
-    for (uint32_t i = gl; i < n4max; i += 4 * G) {
-      float4 r[4];
+    if (n4max <= 4u * G) {                         // kernel-uniform: the whole row is in q already
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        r[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-        const uint32_t v = i + (4 + j) * G;
-        if (v < n4) r[j] = fm_ldg_stream(h4 + v);
-      }
+      for (int j = 0; j < 4; ++j)
+        if (gl + j * G < n4) mom4(m, q[j], pivot);
+    } else {
+      for (uint32_t i = gl; i < n4max; i += 4 * G) {
+        float4 r[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (i + j * G < n4) mom4(m, q[j], pivot);
-        q[j] = r[j];
+        for (int j = 0; j < 4; ++j) {
+          r[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          const uint32_t v = i + (4 + j) * G;
+          if (v < n4) r[j] = fm_ldg_stream(h4 + v);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (i + j * G < n4) mom4(m, q[j], pivot);
+          q[j] = r[j];
+        }
       }
     }
     for (uint32_t t = (n4 << 2) + gl; t < nh; t += G)   // up to three points after the last full vector
@@ -137,20 +143,30 @@ __global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs
       // branch and no index test per point.
       const float up_f = (tp.bound_mask & 1u) ? __double2float_rd(up) : CUDART_INF_F;
       const float lo_f = (tp.bound_mask & 2u) ? __double2float_ru(lo) : -CUDART_INF_F;
+      // lane gl's vector j covers points 4 (gl + j G) ..: the part 4 G j of the bit position is a
+      // compile-time constant (and stays inside one 32-bit word for G <= 8), the part 4 gl is one
+      // shift of each word at the end
+      uint32_t w[2] = {0u, 0u};
       unsigned long long m64 = 0;
 #pragma unroll
       for (int j = 0; j < CV; ++j) {
-        const uint32_t v = gl + j * G;               // float4 number: points 4v .. 4v+3
         const uint32_t nib = ((cq[j].x > up_f || cq[j].x < lo_f) ? 1u : 0u) | ((cq[j].y > up_f || cq[j].y < lo_f) ? 2u : 0u) |
                              ((cq[j].z > up_f || cq[j].z < lo_f) ? 4u : 0u) | ((cq[j].w > up_f || cq[j].w < lo_f) ? 8u : 0u);
-        if (v < 16u) m64 |= (unsigned long long)nib << (4u * v);
+        if constexpr (G <= 8) {
+          if (4 * G * j < 64) w[(4 * G * j) >> 5] |= nib << ((4 * G * j) & 31);
+        } else {
+          const uint32_t v = gl + j * G;             // float4 number: points 4v .. 4v+3
+          if (v < 16u) m64 |= (unsigned long long)nib << (4u * v);
+        }
       }
+      if constexpr (G <= 8) m64 = (unsigned long long)(w[0] << (4 * gl)) | ((unsigned long long)(w[1] << (4 * gl)) << 32);
       if (nc < 64u) m64 &= (1ull << nc) - 1ull;
       mlo = (uint32_t)m64; mhi = (uint32_t)(m64 >> 32);
     }
     mlo = group_or<G>(mlo); mhi = group_or<G>(mhi);
 
-    // ---- a8, a9: verdict, record, roll-up ------------------------------------------------------
+    // ---- a8: verdict, record -------------------------------------------------------------------
+    uint32_t verdict_out = 0xFFu;
     if (live && gl == 0) {
       uint32_t status = 0;
       if (!model_ok) status |= FM_ST_HIST_INSUFFICIENT;
@@ -175,7 +191,23 @@ __global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs
         reinterpret_cast<fm_series_rec*>(a.out)[s] = r;
       }
       if (a.aux) a.aux[s] = fm_rank_aux{0, 0, 0, 0, 0, 0u, 0u};
-      if (a.api && a.api_id) fm_rollup_add(a.api, a.api_id[s], a.n_apis, verdict);
+      verdict_out = verdict;
+    }
+    // ---- a9: roll-up, one add per API and counter among the series of this warp (the series of an
+    // API are neighbours in a batch: 32 / G series usually name one or two APIs)
+    if (a.api && a.api_id) {                       // kernel-uniform
+      if (gl == 0) {
+        constexpr uint32_t leaders = G == 32 ? 1u : (G == 16 ? 0x00010001u : (G == 8 ? 0x01010101u : (G == 4 ? 0x11111111u : 0x55555555u)));
+        const uint32_t id = live ? a.api_id[s] : 0xFFFFFFFFu;
+        const uint32_t peers = __match_any_sync(leaders, id);
+        const uint32_t bad = __ballot_sync(leaders, verdict_out == FM_UNHEALTHY) & peers;
+        const uint32_t unk = __ballot_sync(leaders, verdict_out == FM_UNKNOWN) & peers;
+        if (id < a.n_apis && (peers & ((1u << lane) - 1u)) == 0u) {   // first lane of its API; ids outside the table are dropped
+          atomicAdd(&a.api[id].n_children, (uint32_t)__popc(peers));
+          if (bad) atomicAdd(&a.api[id].n_unhealthy, (uint32_t)__popc(bad));
+          if (unk) atomicAdd(&a.api[id].n_unknown, (uint32_t)__popc(unk));
+        }
+      }
     }
   }
 }
