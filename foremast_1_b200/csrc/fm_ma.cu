@@ -85,7 +85,13 @@ __global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs
     // shorter than one vector fetch it on their own)
     const float p0 = __shfl_sync(FM_FULL, q[0].x, lane & ~(G - 1));
     const double pivot = nh >= 4u ? (double)p0 : (nh ? (double)__ldg(hx) : 0.0);
-    if (n4max <= 4u * G) {                         // kernel-uniform: the whole row is in q already
+#ifndef FM_MA_SHORT
+#define FM_MA_SHORT 1
+#endif
+#ifndef FM_MA_WORDS
+#define FM_MA_WORDS 1
+#endif
+    if (FM_MA_SHORT && n4max <= 4u * G) {          // kernel-uniform: the whole row is in q already
 #pragma unroll
       for (int j = 0; j < 4; ++j)
         if (gl + j * G < n4) mom4(m, q[j], pivot);
@@ -152,14 +158,14 @@ __global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs
       for (int j = 0; j < CV; ++j) {
         const uint32_t nib = ((cq[j].x > up_f || cq[j].x < lo_f) ? 1u : 0u) | ((cq[j].y > up_f || cq[j].y < lo_f) ? 2u : 0u) |
                              ((cq[j].z > up_f || cq[j].z < lo_f) ? 4u : 0u) | ((cq[j].w > up_f || cq[j].w < lo_f) ? 8u : 0u);
-        if constexpr (G <= 8) {
+        if constexpr (FM_MA_WORDS && G <= 8) {
           if (4 * G * j < 64) w[(4 * G * j) >> 5] |= nib << ((4 * G * j) & 31);
         } else {
           const uint32_t v = gl + j * G;             // float4 number: points 4v .. 4v+3
           if (v < 16u) m64 |= (unsigned long long)nib << (4u * v);
         }
       }
-      if constexpr (G <= 8) m64 = (unsigned long long)(w[0] << (4 * gl)) | ((unsigned long long)(w[1] << (4 * gl)) << 32);
+      if constexpr (FM_MA_WORDS && G <= 8) m64 = (unsigned long long)(w[0] << (4 * gl)) | ((unsigned long long)(w[1] << (4 * gl)) << 32);
       if (nc < 64u) m64 &= (1ull << nc) - 1ull;
       mlo = (uint32_t)m64; mhi = (uint32_t)(m64 >> 32);
     }
