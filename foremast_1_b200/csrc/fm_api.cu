@@ -43,6 +43,12 @@ thread_local std::string g_create_error;
 // only rows it does not hold (plus every current row).  One layout (n_base, pitch, n_hist, pitch) at
 // a time; a batch of another layout starts the cache afresh.  Slots are recycled least-recently-
 // scored first (a clock hand over the per-slot epoch of the last call that used it).
+// chunk buffers in flight per ctx: upload of chunk i+2, kernels of chunk i+1, read-back of chunk i
+#ifndef FM_PIPE_SLOTS
+#define FM_PIPE_SLOTS 2
+#endif
+constexpr int kPipe = FM_PIPE_SLOTS;
+
 struct RowCache {
   static constexpr uint32_t kNone = 0xFFFFFFFFu;
   uint64_t max_bytes = 0;
@@ -61,12 +67,17 @@ struct RowCache {
   std::vector<uint8_t> miss;                // per row of the current call: has to be uploaded
   bool prev_clean = false;                  // every row of the previous call was resident when it ended
   bool any_miss = false;
+  uint32_t* pin_slot = nullptr;             // prev_slot in pinned memory: its per-chunk uploads must not
+  size_t pin_cap = 0;                       // stall the host behind the copy stream (pageable copies do)
+  bool pin_fresh = false;                   // pin_slot == prev_slot
   uint64_t hits = 0, misses = 0, evictions = 0, uncached = 0;
 
   void release() {
     if (d_base) cudaFree(d_base);
     if (d_hist) cudaFree(d_hist);
+    if (pin_slot) cudaFreeHost(pin_slot);
     d_base = d_hist = nullptr;
+    pin_slot = nullptr; pin_cap = 0; pin_fresh = false;
     cap = 0; n_live = 0; hand = 0;
     slot_id.clear(); slot_epoch.clear(); slot_blen.clear(); slot_hlen.clear(); slot_live.clear();
     index.clear(); prev_ids.clear(); prev_slot.clear(); miss.clear(); prev_clean = false;
@@ -82,11 +93,11 @@ struct fm_ctx {
   cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_m = nullptr;
   FmParamsDev params;
   FmParamsDev* d_params = nullptr;
-  // staging for fm_score_batch: two chunk slots
-  Arena in[2], out[2], roll, misc, hw;
+  // staging for fm_score_batch: kPipe chunk slots
+  Arena in[kPipe], out[kPipe], roll, misc, hw;
   RowCache cache[2];               // one per row layout (canary rows, history-only rows)
   uint64_t cache_tick = 0, cache_used[2] = {0, 0};
-  cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
+  cudaEvent_t in_ready[kPipe] = {}, in_free[kPipe] = {}, out_ready[kPipe] = {}, out_free[kPipe] = {};
   std::vector<cudaEvent_t> kev;    // per-chunk kernel timing events
   int score_smem_set = 0, groups_smem_set = 0, sort_smem_set = 0, elect_smem_set = 0, count_smem_set = 0;
   // Diagnostic switches, read ONCE when the ctx is created (none is needed in production):
@@ -490,7 +501,7 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
   FM_CKC(cudaEventCreate(&c->ev_a));
   FM_CKC(cudaEventCreate(&c->ev_b));
   FM_CKC(cudaEventCreate(&c->ev_m));
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < kPipe; ++i) {
     FM_CKC(cudaEventCreateWithFlags(&c->in_ready[i], cudaEventDisableTiming));
     FM_CKC(cudaEventCreateWithFlags(&c->in_free[i], cudaEventDisableTiming));
     FM_CKC(cudaEventCreateWithFlags(&c->out_ready[i], cudaEventDisableTiming));
@@ -514,7 +525,7 @@ int32_t fm_ctx_destroy(fm_ctx* c) {
   if (c->s_h2d) cudaStreamSynchronize(c->s_h2d);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->s_d2h) cudaStreamSynchronize(c->s_d2h);
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < kPipe; ++i) {
     c->in[i].release(); c->out[i].release();
     if (c->in_ready[i]) cudaEventDestroy(c->in_ready[i]);
     if (c->in_free[i]) cudaEventDestroy(c->in_free[i]);
@@ -691,6 +702,7 @@ void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t 
     k.any_miss = false;
     return;
   }
+  k.pin_fresh = false;
   if (slot.size() < S) slot.resize(S);
   miss.assign(S, 0);
   k.any_miss = false;
@@ -787,6 +799,16 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
   const std::vector<uint8_t>& miss = kc.miss;
   if (cached) {
     cache_assign(kc, b, row_ids, S, canary);
+    if (!kc.pin_fresh) {
+      if (kc.pin_cap < S) {
+        if (kc.pin_slot) cudaFreeHost(kc.pin_slot);
+        kc.pin_slot = nullptr; kc.pin_cap = 0;
+        FM_CK(c, cudaHostAlloc(reinterpret_cast<void**>(&kc.pin_slot), S * sizeof(uint32_t), cudaHostAllocDefault));
+        kc.pin_cap = S;
+      }
+      memcpy(kc.pin_slot, kc.prev_slot.data(), S * sizeof(uint32_t));
+      kc.pin_fresh = true;
+    }
     // lengths: a resident row keeps the length it was stored with
     if (canary && b->base_len) {
       eff_blen.resize(S);
@@ -800,10 +822,10 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
   const uint32_t* h_blen = cached && !eff_blen.empty() ? eff_blen.data() : b->base_len;
   const uint32_t* h_hlen = cached && !eff_hlen.empty() ? eff_hlen.data() : b->hist_len;
 
-  // chunking: ~64 MB of rows per chunk, two slots in flight
+  // chunking: ~64 MB of rows per chunk, kPipe slots in flight
   const size_t row_bytes = 4 * ((size_t)b->cur_pitch + (canary ? b->base_pitch : 0) + (b->hist ? b->hist_pitch : 0));
   // (with resident rows the copies are small and the per-chunk launches dominate: larger chunks)
-  uint64_t chunk = row_bytes ? (size_t(cached ? 256 : 64) << 20) / row_bytes : S;
+  uint64_t chunk = row_bytes ? (size_t(c->chunk_mb ? c->chunk_mb : (cached ? 256 : 64)) << 20) / row_bytes : S;
   chunk = std::max<uint64_t>(chunk, 2048);
   chunk = std::min<uint64_t>(chunk, S);
   const uint64_t n_chunks = (S + chunk - 1) / chunk;
@@ -824,7 +846,7 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
   const size_t o_rec = 0;
   const size_t o_aux = al(chunk * rsz);
   const size_t out_bytes = o_aux + (out_aux ? al(chunk * sizeof(fm_rank_aux)) : 0);
-  const int slots = n_chunks > 1 ? 2 : 1;
+  const int slots = (int)std::min<uint64_t>(n_chunks, kPipe);
   for (int i = 0; i < slots; ++i) { FM_CK(c, c->in[i].reserve(in_bytes)); FM_CK(c, c->out[i].reserve(out_bytes)); }
   fm_rollup_rec *d_api = nullptr, *d_svc = nullptr;
   uint32_t* d_api_service = nullptr;
@@ -860,12 +882,12 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
     }                                                                                 \
   } while (0)
   for (uint64_t ci = 0; ci < n_chunks; ++ci) {
-    const int s = (int)(ci & 1);
+    const int s = (int)(ci % kPipe);
     const uint64_t s0 = ci * chunk, n = std::min(chunk, S - s0);
     char* din = static_cast<char*>(c->in[s].p);
     char* dout = static_cast<char*>(c->out[s].p);
     // host -> device on the copy stream, once the slot's previous kernel is done
-    if (ci >= 2) FM_CKL(cudaStreamWaitEvent(c->s_h2d, c->in_free[s], 0));
+    if (ci >= kPipe) FM_CKL(cudaStreamWaitEvent(c->s_h2d, c->in_free[s], 0));
     auto up = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
       h2d += bytes;
       return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->s_h2d);
@@ -898,7 +920,7 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
         }
         i = j;
       }
-      FM_CKL(up(din + o_slot, slot.data() + s0, n * 4));
+      FM_CKL(up(din + o_slot, kc.pin_slot + s0, n * 4));
     }
     if (b->cur_len) FM_CKL(up(din + o_clen, b->cur_len + s0, n * 4));
     if (canary && b->base_len) FM_CKL(up(din + o_blen, h_blen + s0, n * 4));
@@ -925,7 +947,7 @@ int32_t score_batch_impl(fm_ctx* c, const fm_batch* b, const uint64_t* row_ids, 
     pl.a.aux = out_aux ? reinterpret_cast<fm_rank_aux*>(dout + o_aux) : nullptr;
     pl.a.api = roll ? d_api : nullptr;
     FM_CKL(cudaStreamWaitEvent(c->stream, c->in_ready[s], 0));
-    if (ci >= 2) FM_CKL(cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
+    if (ci >= kPipe) FM_CKL(cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
     FM_CKL(cudaEventRecord(c->kev[2 * ci], c->stream));
     if (cached) {
       const uint32_t* d_slot = reinterpret_cast<const uint32_t*>(din + o_slot);
@@ -1118,7 +1140,7 @@ int32_t fm_score_groups_device(fm_ctx* c, const fm_group_batch* b, fm_series_rec
 
 // Host rows: the batch is cut at service boundaries into chunks of ~64 MB of rows; the upload of
 // chunk i+1 (copy stream) runs beside the kernels of chunk i (compute stream) and the read-back of
-// chunk i-1 (second copy stream), two buffer slots as in fm_score_batch.
+// chunk i-1 (second copy stream), kPipe buffer slots as in fm_score_batch.
 int32_t fm_score_groups(fm_ctx* c, const fm_group_batch* b, fm_series_rec* out, fm_rollup_rec* out_svc,
                         fm_timing* timing) {
   if (!c) return FM_E_INVALID;
@@ -1170,7 +1192,7 @@ int32_t fm_score_groups(fm_ctx* c, const fm_group_batch* b, fm_series_rec* out, 
   const size_t in_bytes = o;
   const size_t o_svc = al(max_g * sizeof(fm_series_rec));
   const size_t out_bytes = o_svc + al(max_v * sizeof(fm_rollup_rec));
-  const int slots = n_chunks > 1 ? 2 : 1;
+  const int slots = (int)std::min<uint64_t>(n_chunks, kPipe);
   for (int i = 0; i < slots; ++i) { FM_CK(c, c->in[i].reserve(in_bytes)); FM_CK(c, c->out[i].reserve(out_bytes)); }
   while (c->kev.size() < 2 * n_chunks) {
     cudaEvent_t e; FM_CK(c, cudaEventCreate(&e)); c->kev.push_back(e);
@@ -1189,12 +1211,12 @@ int32_t fm_score_groups(fm_ctx* c, const fm_group_batch* b, fm_series_rec* out, 
     }                                                                                 \
   } while (0)
   for (uint64_t ci = 0; ci < n_chunks; ++ci) {
-    const int s = (int)(ci & 1);
+    const int s = (int)(ci % kPipe);
     const uint64_t v0 = cut_v[ci], nv = cut_v[ci + 1] - v0;
     const uint64_t g0 = b->group_offsets[v0], ng = b->group_offsets[v0 + nv] - g0;
     char* din = static_cast<char*>(c->in[s].p);
     char* dout = static_cast<char*>(c->out[s].p);
-    if (ci >= 2) FM_CKL(cudaStreamWaitEvent(c->s_h2d, c->in_free[s], 0));
+    if (ci >= kPipe) FM_CKL(cudaStreamWaitEvent(c->s_h2d, c->in_free[s], 0));
     auto up = [&](size_t off, const void* src, size_t bytes) -> cudaError_t {
       h2d += bytes;
       return cudaMemcpyAsync(din + off, src, bytes, cudaMemcpyHostToDevice, c->s_h2d);
@@ -1216,7 +1238,7 @@ int32_t fm_score_groups(fm_ctx* c, const fm_group_batch* b, fm_series_rec* out, 
     db.hist_len = (b->hist && b->hist_len) ? reinterpret_cast<const uint32_t*>(din + o_hlen) : nullptr;
     db.metric_type = b->metric_type ? reinterpret_cast<const uint8_t*>(din + o_mt) : nullptr;
     FM_CKL(cudaStreamWaitEvent(c->stream, c->in_ready[s], 0));
-    if (ci >= 2) FM_CKL(cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
+    if (ci >= kPipe) FM_CKL(cudaStreamWaitEvent(c->stream, c->out_free[s], 0));
     FM_CKL(cudaEventRecord(c->kev[2 * ci], c->stream));
     const int32_t rc = groups_launch(c, &db, reinterpret_cast<fm_series_rec*>(dout),
                                      out_svc ? reinterpret_cast<fm_rollup_rec*>(dout + o_svc) : nullptr, nullptr, &launches);
