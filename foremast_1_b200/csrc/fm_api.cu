@@ -251,9 +251,20 @@ int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
   // trade-off between overflow rounds and resident warps: DESIGN.md section 5)
   uint32_t slots = c->count_slots ? (uint32_t)c->count_slots : std::max(64u, ((b->n_cur + cap) * 11u / 16u));
   slots = (slots + 3u) & ~3u;
+  const size_t limit = c->smem_optin ? c->smem_optin : 232448;
+  if (!c->count_slots && b->n_base <= 2048u) {
+    // a 16th resident warp is worth more than the last slots (measured, profiles/var_slots.sh: 1440-point
+    // baselines 9.85 ms per 1M series with 896-944 slots and 16 warps, 10.1 ms with 1032 and 15): take
+    // what 16 warps leave if that is still 9/16 of a slot per key
+    const size_t per_warp = (limit / 16) & ~size_t(127);
+    const size_t fixed = fm_canary_count_fixed_bytes() + (size_t)(64 + cap) * 4;
+    if (per_warp > fixed) {
+      const uint32_t s16 = (uint32_t)((per_warp - fixed) / 8) & ~3u;
+      if (s16 < slots && s16 >= (b->n_cur + cap) * 9u / 16u) slots = s16;
+    }
+  }
   a.log_m = slots;
   a.cnt_nv = (uint32_t)nv; a.cnt_ns = (uint32_t)ns;
-  const size_t limit = c->smem_optin ? c->smem_optin : 232448;
   const size_t sm_total = 233472;
   if (!c->count_smem_set) { FM_CK(c, fm_canary_count_smem_attr((int)limit)); c->count_smem_set = 1; }
   fill_common(c, b, true, a);
