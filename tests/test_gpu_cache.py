@@ -126,3 +126,32 @@ def test_cached_multi_chunk_with_rollup():
             got = ctx.score(cur, base, row_ids=ids_of(0, S), **kw)
             assert got["rec"].tobytes() == ref["rec"].tobytes()
             assert (got["api"] == ref["api"]).all() and (got["svc"] == ref["svc"]).all()
+
+
+@pytest.mark.parametrize("n_base,n_hist", [(3000, 0), (10080, 0), (1440, 10080), (0, 60), (0, 1440)])
+def test_resident_rows_are_read_in_place(n_base, n_hist):
+    """k_canary_team (baselines above 2048 points), k_canary_count with a separate history row and
+    k_ma_only take a resident row straight from its cache slot; a cache half the size of the call
+    mixes resident and uploaded rows in one launch, a permuted re-poll scatters the slots."""
+    rng = np.random.default_rng(n_base + n_hist)
+    S = 600
+    d = synth_desc(2, S, 60, max(n_base, 4), max(n_hist, 4))
+    cur, base, hist, mt = synth_host(d)
+    base = base if n_base else None
+    hist = hist if n_hist else None
+    strat = A.FM_STRAT_CANARY if n_base else A.FM_STRAT_HISTORICAL
+    ids = ids_of(7, S)
+    with Context(0) as ctx:
+        g, t = A.default_params()
+        ctx.set_params(g, t)
+        ref = ctx.score(cur, base, hist, strategy=strat, metric_type=mt, want_aux=True)
+        row_bytes = 4 * ((base.shape[1] if n_base else 0) + (hist.shape[1] if n_hist else 0))
+        for budget in (S * row_bytes * 2, S * row_bytes // 2):
+            ctx.cache_configure(budget)
+            for _ in range(3):
+                got = ctx.score(cur, base, hist, strategy=strat, metric_type=mt, want_aux=True, row_ids=ids)
+                assert got["rec"].tobytes() == ref["rec"].tobytes() and got["aux"].tobytes() == ref["aux"].tobytes()
+            perm = rng.permutation(S)
+            got = ctx.score(cur[perm], None if base is None else base[perm], None if hist is None else hist[perm],
+                            strategy=strat, metric_type=mt[perm], want_aux=True, row_ids=ids[perm])
+            assert got["rec"].tobytes() == ref["rec"][perm].tobytes()
