@@ -378,7 +378,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
   // instruction fetches instead of each missing the instruction cache on its own.
   const uint64_t trips = (a.n_series + stride - 1) / stride;
   for (uint64_t trip = 0; trip < trips; ++trip, s += stride) {
-    if (a.n_stages == 2u) asm volatile("bar.sync 0;" ::: "memory");
+    if (a.n_stages == 2u && ((uint32_t)trip & a.sync_mask) == 0u) asm volatile("bar.sync 0;" ::: "memory");
     if (s >= a.n_series) continue;
     const uint32_t nc = row_len(a.cur_len, s, a.n_cur);
     const uint32_t nb = row_len(a.base_len, s, a.n_base);
