@@ -316,7 +316,7 @@ int32_t plan_ma_only(fm_ctx* c, const fm_batch* b, Plan* pl) {
   pl->wpc = 8;
   // persistent grid = the CTAs that are resident at once (64 registers x 256 threads: 4 per SM; the
   // 2-lane form 3 per SM), so that there is no second, partial wave
-  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * (pl->regs <= 2 ? 3 : 4), need));
+  pl->grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)c->num_sms * fm_ma_only_ctas(pl->regs), need));
   pl->fast = true; pl->kind = 4;
   return FM_OK;
 }

@@ -82,6 +82,7 @@ int fm_launch_canary_team(const FmKArgs& a, int warps, int grid, cudaStream_t st
 cudaError_t fm_canary_count_smem_attr(int bytes);
 size_t fm_canary_elect_fixed_bytes();
 int fm_launch_ma_only(const FmKArgs& a, int group, int grid, cudaStream_t st);
+int fm_ma_only_ctas(int group);   // resident CTAs per SM the kernel is built for
 cudaError_t fm_canary_elect_smem_attr(int bytes);
 int fm_launch_rollup_finalize(fm_rollup_rec* api, uint32_t n_apis, const uint32_t* api_service,
                               fm_rollup_rec* svc, uint32_t n_services, cudaStream_t st);

@@ -40,8 +40,14 @@ __device__ __forceinline__ void mom4(FmMom& m, const float4& q, double pivot) {
   fm_mom_add(m, q.x, pivot); fm_mom_add(m, q.y, pivot); fm_mom_add(m, q.z, pivot); fm_mom_add(m, q.w, pivot);
 }
 
+#ifndef FM_MA_CTAS
+#define FM_MA_CTAS 4
+#endif
+// resident CTAs per SM (the register budget follows: 4 -> 64 registers)
+constexpr int ma_ctas(int g) { return g <= 2 ? 3 : FM_MA_CTAS; }
+
 template <int G>
-__global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs a) {
+__global__ void __launch_bounds__(256, ma_ctas(G)) k_ma_only(const FmKArgs a) {
   constexpr int SPW = 32 / G;                    // series per warp
   const int lane = threadIdx.x & 31;
   const int gl = lane & (G - 1), grp = lane / G;
@@ -219,6 +225,8 @@ __global__ void __launch_bounds__(256, (G <= 2 ? 3 : 4)) k_ma_only(const FmKArgs
 }
 
 }  // namespace
+
+int fm_ma_only_ctas(int group) { return ma_ctas(group); }
 
 int fm_launch_ma_only(const FmKArgs& a, int group, int grid, cudaStream_t st) {
   if (group == 2) k_ma_only<2><<<grid, 256, 0, st>>>(a);
