@@ -16,7 +16,7 @@
 // multiset of the sample in a 256-slot hash table in its parking buffer (election: every key stores
 // its bits into its slot if it read it empty, whoever reads its own bits back owns the slot and
 // counts itself with a fire-and-forget shared-memory add; the others try the next multiplier).  With
-// D <= 32 distinct values, one per lane, "points below me" is a D-step loop over the (value, count)
+// D <= 64 distinct values, at most two per lane, "points below me" is a D-step loop over the (value, count)
 // list, which gives 2 * midrank and t^3 - t per value, and every point fetches the midrank of its
 // value from its slot: ~0.5k instructions where sort + park + two searches per point take 2.7k.
 // A sample with more distinct values (or four failed rounds) takes the network: same integers.
@@ -58,6 +58,7 @@ __device__ __forceinline__ uint32_t row_len(const uint32_t* len, uint64_t s, uin
 constexpr uint32_t kSlots = 256u;         // hash slots per warp: values at +0, counts / midranks at +4*kSlots
 constexpr uint32_t kEmpty = 0xFFFFFFFFu;   // a NaN pattern: rows are NaN-free (foremast_cuda.h)
 constexpr int kRounds = 4;
+constexpr uint32_t kMaxDistinct = 64u;     // distinct values the multiset path ranks: two list entries per lane
 static_assert(2u * kSlots * 4u <= 32u * kR * 4u, "the table lives in the warp's parking buffer");
 
 __device__ __forceinline__ uint32_t slot_of(uint32_t tbl_s, float key, uint32_t mult) {
@@ -66,7 +67,7 @@ __device__ __forceinline__ uint32_t slot_of(uint32_t tbl_s, float key, uint32_t 
 
 // 2 * (rank sum) of group k into lane k and the tie term, from the multiset of the pooled sample.
 // s[2k], s[2k+1]: the points lane and lane + 32 of group k (-0 folded into +0), valid: bit r = s[r]
-// is a point, otherwise a copy of some point of the group.  Destroys s.  False: more than 32 distinct values or unplaced keys; nothing returned.
+// is a point, otherwise a copy of some point of the group.  Destroys s.  False: more than 64 distinct values or unplaced keys; nothing returned.
 __device__ __forceinline__ bool ranks_by_multiset(float (&s)[kR], const uint32_t valid, const uint32_t K, const int lane,
                                                   const uint32_t tbl_s, uint32_t& r2_mine, long long& T) {
   __syncwarp();
@@ -160,7 +161,7 @@ __device__ __forceinline__ bool ranks_by_multiset(float (&s)[kR], const uint32_t
     if (lane >= o) incl += u;
   }
   const uint32_t D = __shfl_sync(FM_FULL, incl, 31);
-  if (D > 32u) return false;
+  if (D > kMaxDistinct) return false;
   __syncwarp();                                    // every lane holds its slots: the value half becomes the list
   uint32_t at = tbl_s + (incl - occ) * 8u;
 #pragma unroll
@@ -172,22 +173,39 @@ __device__ __forceinline__ bool ranks_by_multiset(float (&s)[kR], const uint32_t
     }
   }
   __syncwarp();
-  float dv = 0.f;
-  uint32_t dc = 0, dslot = 0;
+  // lane l owns list entries l and l + 32
+  float dv = 0.f, dv2 = 0.f;
+  uint32_t dc = 0, dslot = 0, dc2 = 0, dslot2 = 0;
   if ((uint32_t)lane < D) {
     dv = fm_lds_f32(tbl_s + (uint32_t)lane * 8u);
     const uint32_t w = fm_lds_u32(tbl_s + (uint32_t)lane * 8u + 4u);
     dc = w & 0xFFFFu; dslot = w >> 16;
   }
-  uint32_t less = 0;
-#pragma unroll 2
-  for (uint32_t i = 0; i < D; ++i) {               // broadcast reads
-    const float vi = fm_lds_f32(tbl_s + i * 8u);
-    const uint32_t ci = fm_lds_u32(tbl_s + i * 8u + 4u) & 0xFFFFu;
-    less += (vi < dv) ? ci : 0u;
+  if ((uint32_t)lane + 32u < D) {
+    dv2 = fm_lds_f32(tbl_s + ((uint32_t)lane + 32u) * 8u);
+    const uint32_t w = fm_lds_u32(tbl_s + ((uint32_t)lane + 32u) * 8u + 4u);
+    dc2 = w & 0xFFFFu; dslot2 = w >> 16;
   }
-  T = (long long)__reduce_add_sync(FM_FULL, dc * (dc * dc - 1u));   // sum t^3 - t <= 512^3
+  uint32_t less = 0, less2 = 0;
+  if (D <= 32u) {                                  // warp-uniform
+#pragma unroll 2
+    for (uint32_t i = 0; i < D; ++i) {             // broadcast reads
+      const float vi = fm_lds_f32(tbl_s + i * 8u);
+      const uint32_t ci = fm_lds_u32(tbl_s + i * 8u + 4u) & 0xFFFFu;
+      less += (vi < dv) ? ci : 0u;
+    }
+  } else {
+#pragma unroll 2
+    for (uint32_t i = 0; i < D; ++i) {
+      const float vi = fm_lds_f32(tbl_s + i * 8u);
+      const uint32_t ci = fm_lds_u32(tbl_s + i * 8u + 4u) & 0xFFFFu;
+      less += (vi < dv) ? ci : 0u;
+      less2 += (vi < dv2) ? ci : 0u;
+    }
+  }
+  T = (long long)__reduce_add_sync(FM_FULL, dc * (dc * dc - 1u) + dc2 * (dc2 * dc2 - 1u));   // sum t^3 - t <= 512^3
   if ((uint32_t)lane < D) fm_sts_u32(tbl_s + 4u * kSlots + dslot * 4u, 2u * less + dc + 1u);
+  if ((uint32_t)lane + 32u < D) fm_sts_u32(tbl_s + 4u * kSlots + dslot2 * 4u, 2u * less2 + dc2 + 1u);
   __syncwarp();
   r2_mine = 0;
 #pragma unroll

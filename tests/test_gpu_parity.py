@@ -361,9 +361,9 @@ def test_groups_multi_chunk_pipeline(monkeypatch):
     assert (ref["svc"] == ora["svc"]).all()
 
 
-@pytest.mark.parametrize("distinct", [1, 2, 7, 31, 32, 33, 40, 64, 200])
+@pytest.mark.parametrize("distinct", [1, 2, 7, 31, 32, 33, 40, 63, 64, 65, 100, 200])
 def test_groups_distinct_values(ctx, distinct):
-    """The rollover kernel ranks a pooled sample with at most 32 distinct values from a hash multiset and
+    """The rollover kernel ranks a pooled sample with at most 64 distinct values from a hash multiset and
     anything else with the sorting network: both sides of that limit, values that collide in the table
     (many services, arbitrary bit patterns), +-0, +-inf and denormals as values, ragged and empty groups."""
     rng = np.random.default_rng(4000 + distinct)
