@@ -110,6 +110,7 @@ struct fm_ctx {
   int ma_group = 0;                // FOREMAST_CUDA_MA_GROUP=4|8|16|32: lanes per series of k_ma_only
   int small_table = 0;             // FOREMAST_CUDA_SMALL_TABLE: elect path, load factor <= 0.8
   int count_sync = 4;              // FOREMAST_CUDA_COUNT_SYNC: trips between two CTA barriers of k_canary_count (power of two)
+  int tie_runs = 24;               // FOREMAST_CUDA_TIE_RUNS: see FmKArgs::tie_runs (0 switches the class path off)
   int force_gather = 0;            // FOREMAST_CUDA_GATHER: cached rows are copied into the chunk even for kernels that read the cache in place
   int chunk_mb = 0;                // FOREMAST_CUDA_CHUNK_MB: rows per pipelined chunk of fm_score_groups (default 64 MB)
   std::string err;
@@ -288,6 +289,7 @@ int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
   // fetches of the long loop body (+4 %); FOREMAST_CUDA_STAGES=1 (experiment): several free-running CTAs
   a.n_stages = c->force_stages == 1 ? 1u : 2u;
   a.sync_mask = (uint32_t)c->count_sync - 1u;
+  a.tie_runs = (uint32_t)c->tie_runs;
   const int w_hi = a.n_stages == 2u ? 16 : 8, w_lo = a.n_stages == 2u ? 2 : 1;
   for (int w = w_lo; w <= w_hi; ++w) {
     const size_t cta = (size_t)w * a.warp_bytes;
@@ -507,6 +509,7 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
   if (const char* e = getenv("FOREMAST_CUDA_MA_GROUP")) { const int v = atoi(e); c->ma_group = (v == 2 || v == 4 || v == 8 || v == 16 || v == 32) ? v : 0; }
   c->small_table = getenv("FOREMAST_CUDA_SMALL_TABLE") != nullptr;
   c->force_gather = getenv("FOREMAST_CUDA_GATHER") != nullptr;
+  if (const char* e = getenv("FOREMAST_CUDA_TIE_RUNS")) { const int v = atoi(e); if (v >= 0 && v <= 65) c->tie_runs = v; }
   if (const char* e = getenv("FOREMAST_CUDA_COUNT_SYNC")) { const int v = atoi(e); if (v >= 1 && v <= 1024 && (v & (v - 1)) == 0) c->count_sync = v; }
   if (const char* e = getenv("FOREMAST_CUDA_CHUNK_MB")) { const int v = atoi(e); c->chunk_mb = (v >= 1 && v <= 4096) ? v : 0; }
   FM_CKC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));

@@ -339,6 +339,105 @@ __device__ __forceinline__ void finish_stats(const FmKArgs& a, const fm_global_p
   }
 }
 
+// ---- heavy ties: the rank integers from the multiset alone -----------------------------------
+// An error-count series (a quarter of a job's metrics) has a handful of distinct values.  When the
+// sorted current row shows few of them, the series first tries this path instead of sweep 2: every
+// key reads its slot (pass A has run) and, if its class owns it, adds itself to the slot's counter
+// with a fire-and-forget red (baseline points in the low half, current points in the high half);
+// no search, no returned atomic, no overflow list.  If every key was placed and the table holds at
+// most 64 classes, the (value, counts) list goes into the consumed stage, lane l takes entries l
+// and l + 32, and one loop over the list gives, per class j with t_j = c_j + b_j points and L_j
+// points below it:  2 R1 = sum c_j (2 L_j + t_j + 1),  T = sum t_j^3 - t_j  -- the same integers as
+// the search path.  Anything else (a lost election, more classes) clears the counters again and
+// returns false: the series then takes sweep 2 as if nothing had happened (the values are intact).
+constexpr uint32_t kTieClasses = 64u;
+struct TieOut { long long r2c, T; bool ok; };
+__device__ __noinline__ TieOut ranks_by_classes(uint32_t stage_s, uint32_t base_s, uint32_t tbl_s, uint32_t c_off,
+                                                uint32_t m_slots, uint32_t NV, uint32_t NS, uint32_t nb, uint32_t hka,
+                                                uint32_t hkb, bool va, bool vb, int lane) {
+  TieOut out = {0, 0, false};
+  const uint32_t mult0 = mult_of(0);
+  uint32_t lost = 0;
+  auto place = [&](uint32_t bits, uint32_t add, bool real) {
+    const uint32_t h = tbl_s + slot_of(bits, mult0, m_slots);
+    const bool won = fm_lds_u32(h) == bits;
+    fm_reds_add(h + c_off, (won && real) ? add : 0u);
+    lost |= (real && !won) ? 1u : 0u;
+  };
+  place(hka, 0x10000u, va);
+  place(hkb, 0x10000u, vb);
+#pragma unroll 1
+  for (uint32_t c = 0; c < NV; ++c) {
+    const uint32_t e0 = ((uint32_t)lane + 32u * c) << 2;
+    const float4 q = fm_lds_v4(base_s + (e0 << 2));
+    place(__float_as_uint(q.x + 0.0f), 1u, e0 < nb);
+    place(__float_as_uint(q.y + 0.0f), 1u, e0 + 1u < nb);
+    place(__float_as_uint(q.z + 0.0f), 1u, e0 + 2u < nb);
+    place(__float_as_uint(q.w + 0.0f), 1u, e0 + 3u < nb);
+  }
+#pragma unroll 1
+  for (uint32_t j = 0; j < NS; ++j) {
+    const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
+    const float q = fm_lds_f32(base_s + (min(e, 128u * NV + 32u * NS - 1u) << 2));
+    place(__float_as_uint(q + 0.0f), 1u, e < nb);
+  }
+  __syncwarp();
+  // occupied slots -> dense list in the stage (every lane scans its share of the counters)
+  uint32_t occ = 0;
+  bool fail = __any_sync(FM_FULL, lost != 0u);
+  if (!fail) {
+    for (uint32_t o = (uint32_t)lane * 16u; o < c_off; o += 512u) {
+      const float4 w = fm_lds_v4(tbl_s + c_off + o);
+      occ += (__float_as_uint(w.x) ? 1u : 0u) + (__float_as_uint(w.y) ? 1u : 0u) + (__float_as_uint(w.z) ? 1u : 0u) +
+             (__float_as_uint(w.w) ? 1u : 0u);
+    }
+    uint32_t incl = occ;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t u = __shfl_up_sync(FM_FULL, incl, d);
+      if (lane >= d) incl += u;
+    }
+    const uint32_t D = __shfl_sync(FM_FULL, incl, 31);
+    fail = D > kTieClasses;
+    if (!fail) {
+      uint32_t at = stage_s + (incl - occ) * 8u;
+      for (uint32_t o = (uint32_t)lane * 16u; o < c_off; o += 512u) {
+        const float4 w = fm_lds_v4(tbl_s + c_off + o);
+        const uint32_t ww[4] = {__float_as_uint(w.x), __float_as_uint(w.y), __float_as_uint(w.z), __float_as_uint(w.w)};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (ww[i]) { sts_v2(at, fm_lds_u32(tbl_s + o + 4u * i), ww[i]); at += 8u; }
+      }
+      __syncwarp();
+      float v0 = 0.f, v1 = 0.f;
+      uint32_t w0 = 0, w1 = 0;
+      if ((uint32_t)lane < D) { const uint2 e = lds_v2(stage_s + 8u * lane); v0 = __uint_as_float(e.x); w0 = e.y; }
+      if ((uint32_t)lane + 32u < D) { const uint2 e = lds_v2(stage_s + 8u * (lane + 32u)); v1 = __uint_as_float(e.x); w1 = e.y; }
+      uint32_t l0 = 0, l1 = 0;
+#pragma unroll 2
+      for (uint32_t i = 0; i < D; ++i) {               // broadcast reads
+        const uint2 e = lds_v2(stage_s + 8u * i);
+        const uint32_t t = (e.y & 0xFFFFu) + (e.y >> 16);
+        const float vi = __uint_as_float(e.x);
+        l0 += (vi < v0) ? t : 0u;
+        l1 += (vi < v1) ? t : 0u;
+      }
+      const uint32_t t0 = (w0 & 0xFFFFu) + (w0 >> 16), t1 = (w1 & 0xFFFFu) + (w1 >> 16);
+      const uint32_t r2 = (w0 >> 16) * (2u * l0 + t0 + 1u) + (w1 >> 16) * (2u * l1 + t1 + 1u);
+      const unsigned long long tt = (unsigned long long)t0 * t0 * t0 - t0 + (unsigned long long)t1 * t1 * t1 - t1;
+      out.r2c = (long long)__reduce_add_sync(FM_FULL, r2);
+      out.T = fm_warp_sum((long long)tt);
+      out.ok = true;
+    }
+  }
+  if (fail) {                                       // sweep 2 expects empty counters
+    __syncwarp();
+    for (uint32_t o = (uint32_t)lane * 16u; o < c_off; o += 512u) sts_zero16(tbl_s + c_off + o);
+  }
+  __syncwarp();
+  return out;
+}
+
 struct ModelOut { double mean, sigma; bool ok; };
 __device__ __noinline__ ModelOut model_call(const fm_global_params* g, const float* x, uint32_t n, bool vec_ok, int lane) {
   ModelOut o;
@@ -500,6 +599,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
       // ---- sorted current row -> search table --------------------------------------------------
       float sa = ca, sb = cb;
       sort64(sa, sb, lane);
+      uint32_t cur_runs;                                  // distinct values of the current row (+1 for its padding)
       {
         const float qa = __shfl_up_sync(FM_FULL, sa, 1);
         const float last_a = __shfl_sync(FM_FULL, sa, 31);
@@ -508,6 +608,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
         const uint32_t ba = __ballot_sync(FM_FULL, lane == 0 || qa != sa), bb = __ballot_sync(FM_FULL, qb != sb);
         uint32_t lo_a, e_a, lo_b, e_b;
         runs_from_ballots(ba, bb, lane, lo_a, e_a, lo_b, e_b);
+        cur_runs = (uint32_t)__popc(ba) + (uint32_t)__popc(bb);
         // run length counts real samples only (the +inf padding behind position nc is not a sample)
         const uint32_t rl_a = min(e_a, nc) - min(lo_a, nc), rl_b = min(e_b, nc) - min(lo_b, nc);
         fm_sts_f32(search_s + 4u * lane, sa);
@@ -522,6 +623,12 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
       // one entry per key it has consumed, entry k of a lane sits in stage word 32 k + lane, and the
       // 2 + 4 c + 4 rows of 32 words behind vector row c have been read by every lane by then.
       __syncwarp();                                         // pass A and the search table are complete
+      bool tie_done = false;
+      if (cur_runs <= a.tie_runs && 2u * cur_runs <= nc) {  // few distinct current values, most of them repeated: probably an error-count series
+        const TieOut to = ranks_by_classes(stage_s, base_s, tbl_s, c_off, m_slots, NV, NS, nb, hka, hkb, va, vb, lane);
+        if (to.ok) { r2c = to.r2c; Tt = to.T; ax.r2_cur = r2c; ax.t_mw = Tt; tie_done = true; }
+      }
+      if (!tie_done) {
       Tie tie = {0u, 0u};
       const uint32_t list0 = stage_s + 4u * lane;
       uint32_t lptr = list0;
@@ -619,6 +726,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
       const unsigned long long ninv = (unsigned long long)(kCap - nb) + (64u - nc);
       Tt = (long long)(3ull * t3 + (unsigned long long)fm_warp_sum((long long)t_extra) - (ninv * ninv * ninv - ninv));
       ax.r2_cur = r2c; ax.t_mw = Tt;
+      }
     }
 
     // the stage (rows, then lists) has been consumed: hand it to the TMA unit for the next series

@@ -43,6 +43,7 @@ struct FmKArgs {
   // k_canary_team and k_ma_only: series s takes its baseline / history row from slot row_slot[s] of
   // the cache unless that is 0xFFFFFFFF (row not resident: it is in base / hist like any other)
   uint32_t sync_mask;      // k_canary_count: CTA barrier on trips with (trip & sync_mask) == 0
+  uint32_t tie_runs;       // k_canary_count: current rows with at most this many distinct values try the class path (0: off)
   const uint32_t* row_slot;
   const float* cache_base;
   const float* cache_hist;
