@@ -202,6 +202,85 @@ __device__ __forceinline__ void classify(const uint32_t* bits, uint32_t tbl_s, u
   for (int k = 0; k < G; ++k) { t.sq += c[k] * c[k]; t.lin += c[k]; }
 }
 
+// ---- singleton filter (FM_COUNT_PREFILTER) ------------------------------------------------------
+// Most keys of a continuous series are the only one of their value, and such a key adds nothing to
+// the tie term.  Sweep 1 therefore does not elect anything: every key adds 1 to a 16-bit counter
+// picked by a hash of its bits (fire-and-forget red; the whole table region serves as 4 x slots
+// counters).  In sweep 2 a key whose counter reads 1 shares its hash, hence its value, with nobody
+// and is done; the others (a third of a continuous row: hash neighbours, and every real tie) go to
+// the lists, and only they run the election rounds.  Exact: a counter never under-counts, and
+// 16 bits hold every possible class (a row has at most 2111 keys).
+#ifndef FM_COUNT_PREFILTER
+#define FM_COUNT_PREFILTER 1
+#endif
+constexpr uint32_t kCntMult = 0x85EBCA6Bu;
+__device__ __forceinline__ uint32_t cnt_addr(uint32_t tbl_s, uint32_t bits, uint32_t m16, uint32_t& sh) {
+  const uint32_t i = __umulhi(bits * kCntMult, m16);
+  sh = (i & 1u) << 4;
+  return tbl_s + ((i >> 1) << 2);
+}
+__device__ __forceinline__ void cnt_add(uint32_t tbl_s, uint32_t bits, uint32_t m16) {
+  uint32_t sh;
+  const uint32_t a = cnt_addr(tbl_s, bits, m16, sh);
+  fm_reds_add(a, 1u << sh);
+}
+// list entry for a key unless it is alone on its counter (w = the counter word)
+__device__ __forceinline__ void list_unless_single(uint32_t w, uint32_t sh, uint32_t bits, uint32_t& lptr) {
+  const uint32_t many = ((w >> sh) & 0xFFFFu) > 1u ? 0xFFFFFFFFu : 0u;
+  fm_sts_u32(lptr, bits);
+  lptr += 128u & many;
+}
+// rank_group without the election: search + singleton test
+template <int G>
+__device__ __forceinline__ void rank_group_p(const float* x, uint32_t search_lo, uint32_t search_hi, uint32_t final_k,
+                                             float c31, uint32_t tbl_s, uint32_t m16, uint32_t& acc_all,
+                                             uint32_t& acc_eq, uint32_t& lptr) {
+  uint32_t addr[G], h[G], sh[G], vv[G];
+#pragma unroll
+  for (int k = 0; k < G; ++k) {
+    addr[k] = (c31 < x[k]) ? search_hi : search_lo;
+    h[k] = cnt_addr(tbl_s, __float_as_uint(x[k]), m16, sh[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < G; ++k) vv[k] = fm_lds_u32(h[k]);
+  {
+    float v[G];
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 60u);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<64u>(addr[k], v[k], x[k]);
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 28u);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<32u>(addr[k], v[k], x[k]);
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 12u);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<16u>(addr[k], v[k], x[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < G; ++k) list_unless_single(vv[k], sh[k], __float_as_uint(x[k]), lptr);
+  {
+    float v[G];
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 4u);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<8u>(addr[k], v[k], x[k]);
+#pragma unroll
+    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k]);
+#pragma unroll
+    for (int k = 0; k < G; ++k) step_lt<4u>(addr[k], v[k], x[k]);
+  }
+  uint2 w[G];
+#pragma unroll
+  for (int k = 0; k < G; ++k) w[k] = lds_v2(final_k + 2u * addr[k]);
+#pragma unroll
+  for (int k = 0; k < G; ++k) {
+    acc_all += w[k].y;
+    if (__uint_as_float(w[k].x) == x[k]) acc_eq += w[k].y;
+  }
+}
+
 // vector row c of the staged baseline: lane l takes float4 number l + 32 c (conflict-free).  Returns
 // the index of its first element; k = the four keys (-0 folded onto +0, missing points = the NaN
 // pattern), q = the raw samples.
@@ -525,6 +604,35 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
       model_ok = mo.ok; rec.mean = mo.mean; rec.sigma = mo.sigma;
     }
 
+    // ---- sorted current row -> search table (before sweep 1: what the row looks like decides what
+    // sweep 1 builds) ------------------------------------------------------------------------------
+    uint32_t cur_runs = 65u;                              // distinct values of the current row (+1 for its padding)
+    float c31 = 0.f;
+    if (ranks) {
+      float sa = ca, sb = cb;
+      sort64(sa, sb, lane);
+      {
+        const float qa = __shfl_up_sync(FM_FULL, sa, 1);
+        const float last_a = __shfl_sync(FM_FULL, sa, 31);
+        float qb = __shfl_up_sync(FM_FULL, sb, 1);
+        if (lane == 0) qb = last_a;
+        const uint32_t ba = __ballot_sync(FM_FULL, lane == 0 || qa != sa), bb = __ballot_sync(FM_FULL, qb != sb);
+        uint32_t lo_a, e_a, lo_b, e_b;
+        runs_from_ballots(ba, bb, lane, lo_a, e_a, lo_b, e_b);
+        cur_runs = (uint32_t)__popc(ba) + (uint32_t)__popc(bb);
+        // run length counts real samples only (the +inf padding behind position nc is not a sample)
+        const uint32_t rl_a = min(e_a, nc) - min(lo_a, nc), rl_b = min(e_b, nc) - min(lo_b, nc);
+        fm_sts_f32(search_s + 4u * lane, sa);
+        fm_sts_f32(search_s + 4u * (lane + 33u), sb);
+        sts_v2(final_s + 8u * lane, __float_as_uint(sa), (rl_a << 16) | (2u * lane));
+        sts_v2(final_s + 8u * (lane + 33u), __float_as_uint(sb), (rl_b << 16) | (2u * (lane + 32u)));
+      }
+      c31 = __shfl_sync(FM_FULL, sa, 31);
+    }
+    // few distinct current values, most of them repeated: probably an error-count series, whose rank
+    // integers come from its classes (ranks_by_classes): sweep 1 then elects instead of counting
+    const bool tie_cand = ranks && cur_runs <= a.tie_runs && 2u * cur_runs <= nc;
+
     // ---- sweep 1 over the staged baseline: moments, election pass A -------------------------------
     // (the keys are NOT kept: sweep 2 reads the stage again, so that a lane holds a few keys at a
     // time and both sweeps are short rolled loops that stay in the instruction cache)
@@ -534,10 +642,25 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
     const uint32_t mult0 = mult_of(0);
     const uint32_t hka = va ? __float_as_uint(ca) : kNoKey, hkb = vb ? __float_as_uint(cb) : kNoKey;
     const uint32_t nfull = min(NV, nb >> 7);                  // vector rows without a missing point
+    const uint32_t m16 = 4u * m_slots;                        // 16-bit counters in the table region
+    auto cnt_add_all = [&](uint32_t bits) { cnt_add(tbl_s, bits, 4u * m_slots); };
+    auto pass_a = [&](uint32_t bits) {                        // sweep 1's part of the multiset
+#if FM_COUNT_PREFILTER
+      if (tie_cand) fm_sts_u32(tbl_s + slot_of(bits, mult0, m_slots), bits);
+      else cnt_add(tbl_s, bits, m16);
+#else
+      fm_sts_u32(tbl_s + slot_of(bits, mult0, m_slots), bits);
+#endif
+    };
     if (ranks) {
+#if FM_COUNT_PREFILTER
+      for (uint32_t o = (uint32_t)lane * 16u; o < 2u * c_off; o += 512u) sts_zero16(tbl_s + o);
+      __syncwarp();
+#else
       for (uint32_t o = (uint32_t)lane * 16u; o < c_off; o += 512u) sts_zero16(tbl_s + c_off + o);
-      fm_sts_u32(tbl_s + slot_of(hka, mult0, m_slots), hka);
-      fm_sts_u32(tbl_s + slot_of(hkb, mult0, m_slots), hkb);
+#endif
+      pass_a(hka);
+      pass_a(hkb);
     }
     if (ranks || fuse_model) {
       auto row1 = [&](uint32_t c) {
@@ -549,10 +672,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
         if (ranks) {
           const uint32_t k0 = __float_as_uint(q.x + 0.0f), k1 = __float_as_uint(q.y + 0.0f),
                          k2 = __float_as_uint(q.z + 0.0f), k3 = __float_as_uint(q.w + 0.0f);
-          fm_sts_u32(tbl_s + slot_of(k0, mult0, m_slots), k0);
-          fm_sts_u32(tbl_s + slot_of(k1, mult0, m_slots), k1);
-          fm_sts_u32(tbl_s + slot_of(k2, mult0, m_slots), k2);
-          fm_sts_u32(tbl_s + slot_of(k3, mult0, m_slots), k3);
+          pass_a(k0); pass_a(k1); pass_a(k2); pass_a(k3);
         }
       };
 #pragma unroll 1
@@ -570,7 +690,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
         }
         if (ranks) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) fm_sts_u32(tbl_s + slot_of(__float_as_uint(k[i]), mult0, m_slots), __float_as_uint(k[i]));
+          for (int i = 0; i < 4; ++i) pass_a(__float_as_uint(k[i]));
         }
       }
 #pragma unroll 1
@@ -582,7 +702,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
           v = q + 0.0f;
           if (fuse_model) fm_mom_add(mom, q, pivot);
         }
-        if (ranks) fm_sts_u32(tbl_s + slot_of(__float_as_uint(v), mult0, m_slots), __float_as_uint(v));
+        if (ranks) pass_a(__float_as_uint(v));
       }
     }
     if (a.hist) {
@@ -596,27 +716,6 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
 
     long long r2c = 0, Tt = 0;
     if (ranks) {
-      // ---- sorted current row -> search table --------------------------------------------------
-      float sa = ca, sb = cb;
-      sort64(sa, sb, lane);
-      uint32_t cur_runs;                                  // distinct values of the current row (+1 for its padding)
-      {
-        const float qa = __shfl_up_sync(FM_FULL, sa, 1);
-        const float last_a = __shfl_sync(FM_FULL, sa, 31);
-        float qb = __shfl_up_sync(FM_FULL, sb, 1);
-        if (lane == 0) qb = last_a;
-        const uint32_t ba = __ballot_sync(FM_FULL, lane == 0 || qa != sa), bb = __ballot_sync(FM_FULL, qb != sb);
-        uint32_t lo_a, e_a, lo_b, e_b;
-        runs_from_ballots(ba, bb, lane, lo_a, e_a, lo_b, e_b);
-        cur_runs = (uint32_t)__popc(ba) + (uint32_t)__popc(bb);
-        // run length counts real samples only (the +inf padding behind position nc is not a sample)
-        const uint32_t rl_a = min(e_a, nc) - min(lo_a, nc), rl_b = min(e_b, nc) - min(lo_b, nc);
-        fm_sts_f32(search_s + 4u * lane, sa);
-        fm_sts_f32(search_s + 4u * (lane + 33u), sb);
-        sts_v2(final_s + 8u * lane, __float_as_uint(sa), (rl_a << 16) | (2u * lane));
-        sts_v2(final_s + 8u * (lane + 33u), __float_as_uint(sb), (rl_b << 16) | (2u * (lane + 32u)));
-      }
-      const float c31 = __shfl_sync(FM_FULL, sa, 31);
 
       // ---- sweep 2: every key's place in the sorted current row + election pass B ---------------
       // The overflow lists grow into the stage BEHIND the read position: a lane has produced at most
@@ -624,9 +723,31 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
       // 2 + 4 c + 4 rows of 32 words behind vector row c have been read by every lane by then.
       __syncwarp();                                         // pass A and the search table are complete
       bool tie_done = false;
-      if (cur_runs <= a.tie_runs && 2u * cur_runs <= nc) {  // few distinct current values, most of them repeated: probably an error-count series
+      if (tie_cand) {
         const TieOut to = ranks_by_classes(stage_s, base_s, tbl_s, c_off, m_slots, NV, NS, nb, hka, hkb, va, vb, lane);
         if (to.ok) { r2c = to.r2c; Tt = to.T; ax.r2_cur = r2c; ax.t_mw = Tt; tie_done = true; }
+#if FM_COUNT_PREFILTER
+        else {                                              // the class path used the table: count again
+          for (uint32_t o = (uint32_t)lane * 16u; o < 2u * c_off; o += 512u) sts_zero16(tbl_s + o);
+          __syncwarp();
+          cnt_add_all(hka);
+          cnt_add_all(hkb);
+#pragma unroll 1
+          for (uint32_t c = 0; c < NV; ++c) {
+            float k[4];
+            float4 q;
+            keys4(base_s, c, lane, nb, nokey, k, q);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) cnt_add_all(__float_as_uint(k[i]));
+          }
+#pragma unroll 1
+          for (uint32_t j = 0; j < NS; ++j) {
+            const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
+            cnt_add_all(__float_as_uint(e < nb ? fm_lds_f32(base_s + (e << 2)) + 0.0f : nokey));
+          }
+          __syncwarp();
+        }
+#endif
       }
       if (!tie_done) {
       Tie tie = {0u, 0u};
@@ -634,17 +755,29 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
       uint32_t lptr = list0;
       uint32_t acc_all = 0, acc_eq = 0;
       const uint32_t final_k = final_s - 2u * search_s;     // entry address = final_k + 2 * probe address
+#if FM_COUNT_PREFILTER
+      {
+        uint32_t sha, shb;
+        const uint32_t aa = cnt_addr(tbl_s, hka, m16, sha), ab = cnt_addr(tbl_s, hkb, m16, shb);
+        const uint32_t wa = fm_lds_u32(aa), wb = fm_lds_u32(ab);
+        list_unless_single(wa, sha, hka, lptr);
+        list_unless_single(wb, shb, hkb, lptr);
+      }
+#define FM_RANK_GROUP(G, K) rank_group_p<G>(K, search_s, search_s + 132u, final_k, c31, tbl_s, m16, acc_all, acc_eq, lptr)
+#else
       {
         const uint32_t ck[2] = {hka, hkb};
         classify<2>(ck, tbl_s, c_off, mult0, m_slots, tie, lptr);
       }
+#define FM_RANK_GROUP(G, K) rank_group<G>(K, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr)
+#endif
       uint32_t c = 0;
       auto rows2 = [&](uint32_t cc) {                         // two full vector rows: eight probe chains in flight
         const float4 q0 = fm_lds_v4(base_s + (((uint32_t)lane + 32u * cc) << 4));
         const float4 q1 = fm_lds_v4(base_s + (((uint32_t)lane + 32u * cc + 32u) << 4));
         const float k[8] = {q0.x + 0.0f, q0.y + 0.0f, q0.z + 0.0f, q0.w + 0.0f,
                             q1.x + 0.0f, q1.y + 0.0f, q1.z + 0.0f, q1.w + 0.0f};
-        rank_group<8>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
+        FM_RANK_GROUP(8, k);
       };
 #pragma unroll 1
       for (; c + 2u <= nfull; c += 2u) rows2(c);
@@ -653,15 +786,16 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
         float k[4];
         float4 q;
         keys4(base_s, c, lane, nb, nokey, k, q);
-        rank_group<4>(k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
+        FM_RANK_GROUP(4, k);
       }
 #pragma unroll 1
       for (uint32_t j = 0; j < NS; ++j) {
         const uint32_t e = 128u * NV + (uint32_t)lane + 32u * j;
         const float k = e < nb ? fm_lds_f32(base_s + (e << 2)) + 0.0f : nokey;
-        rank_group<1>(&k, search_s, search_s + 132u, final_k, c31, tbl_s, c_off, mult0, m_slots, acc_all, acc_eq, tie, lptr);
+        FM_RANK_GROUP(1, &k);
       }
 
+#undef FM_RANK_GROUP
       // ---- overflow rounds -------------------------------------------------------------------------
       uint32_t n_l = (lptr - list0) >> 7;
       unsigned long long t_extra = 0;
