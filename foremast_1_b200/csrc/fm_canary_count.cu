@@ -233,7 +233,7 @@ __device__ __forceinline__ void list_unless_single(uint32_t w, uint32_t sh, uint
 // rank_group without the election: search + singleton test
 template <int G>
 __device__ __forceinline__ void rank_group_p(const float* x, uint32_t search_lo, uint32_t search_hi, uint32_t final_k,
-                                             float c31, uint32_t tbl_s, uint32_t m16, uint32_t& acc_all,
+                                             float c31, float c15, float c47, uint32_t tbl_s, uint32_t m16, uint32_t& acc_all,
                                              uint32_t& acc_eq, uint32_t& lptr) {
   uint32_t addr[G], h[G], sh[G], vv[G];
 #pragma unroll
@@ -241,14 +241,15 @@ __device__ __forceinline__ void rank_group_p(const float* x, uint32_t search_lo,
     addr[k] = (c31 < x[k]) ? search_hi : search_lo;
     h[k] = cnt_addr(tbl_s, __float_as_uint(x[k]), m16, sh[k]);
   }
+  float top[G];                                    // second level from registers: the key is c15 or c47
+#pragma unroll
+  for (int k = 0; k < G; ++k) top[k] = (c31 < x[k]) ? c47 : c15;
 #pragma unroll
   for (int k = 0; k < G; ++k) vv[k] = fm_lds_u32(h[k]);
   {
     float v[G];
 #pragma unroll
-    for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 60u);
-#pragma unroll
-    for (int k = 0; k < G; ++k) step_lt<64u>(addr[k], v[k], x[k]);
+    for (int k = 0; k < G; ++k) step_lt<64u>(addr[k], top[k], x[k]);
 #pragma unroll
     for (int k = 0; k < G; ++k) v[k] = fm_lds_f32(addr[k] + 28u);
 #pragma unroll
@@ -607,7 +608,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
     // ---- sorted current row -> search table (before sweep 1: what the row looks like decides what
     // sweep 1 builds) ------------------------------------------------------------------------------
     uint32_t cur_runs = 65u;                              // distinct values of the current row (+1 for its padding)
-    float c31 = 0.f;
+    float c31 = 0.f, c15 = 0.f, c47 = 0.f;
     if (ranks) {
       float sa = ca, sb = cb;
       sort64(sa, sb, lane);
@@ -628,6 +629,8 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
         sts_v2(final_s + 8u * (lane + 33u), __float_as_uint(sb), (rl_b << 16) | (2u * (lane + 32u)));
       }
       c31 = __shfl_sync(FM_FULL, sa, 31);
+      c15 = __shfl_sync(FM_FULL, sa, 15);
+      c47 = __shfl_sync(FM_FULL, sb, 15);
     }
     // few distinct current values, most of them repeated: probably an error-count series, whose rank
     // integers come from its classes (ranks_by_classes): sweep 1 then elects instead of counting
@@ -763,7 +766,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
         list_unless_single(wa, sha, hka, lptr);
         list_unless_single(wb, shb, hkb, lptr);
       }
-#define FM_RANK_GROUP(G, K) rank_group_p<G>(K, search_s, search_s + 132u, final_k, c31, tbl_s, m16, acc_all, acc_eq, lptr)
+#define FM_RANK_GROUP(G, K) rank_group_p<G>(K, search_s, search_s + 132u, final_k, c31, c15, c47, tbl_s, m16, acc_all, acc_eq, lptr)
 #else
       {
         const uint32_t ck[2] = {hka, hkb};
