@@ -213,13 +213,16 @@ def secondary(ctx, sampler, peak, steps=5, warmup=3):
         for _ in range(warmup):
             run()
         ctx.sync()
+        # at least `steps` runs and at least ~0.25 s of them, so that the clock sampler sees the case
+        # under load (a 0.1 ms kernel timed five times would be over before its first sample)
+        n = max(steps, min(2000, int(250.0 / max(t.main_kernel_ms, 1e-3))))
         t0 = time.perf_counter()
         ms = []
-        for _ in range(steps):
+        for _ in range(n):
             run()
             ms.append(t.main_kernel_ms)
         ctx.sync()
-        return statistics.median(ms), sampler.window(t0, time.perf_counter())
+        return statistics.median(ms), dict(sampler.window(t0, time.perf_counter()), runs=n)
 
     def series_case(name, config, S, n_cur, n_base, n_hist, mode, canary, compact, rollup):
         g, _ = A.default_params()

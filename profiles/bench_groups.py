@@ -14,6 +14,7 @@ from foremast_1_b200.engine import Context, synth_desc  # noqa: E402
 V = int(sys.argv[1]) if len(sys.argv) > 1 else 100_000
 NH = int(sys.argv[2]) if len(sys.argv) > 2 else 1440          # history points (0: no model)
 MODE = sys.argv[3] if len(sys.argv) > 3 else "KRUSKAL"     # KRUSKAL | NONE
+PAD = int(sys.argv[4]) if len(sys.argv) > 4 else 0          # bytes allocated first (shifts every buffer: placement effects)
 rng = np.random.default_rng(44)
 K = rng.integers(3, 9, V)
 off = np.concatenate([[0], np.cumsum(K)]).astype(np.uint32)
@@ -25,6 +26,7 @@ with Context(0) as ctx:
     g, t = A.default_params()
     g.pairwise_mode = A.FM_PW_KRUSKAL if MODE == "KRUSKAL" else A.FM_PW_NONE
     ctx.set_params(g, t)
+    d_pad = ctx.dev_alloc(PAD) if PAD else None
     d_ids, d_hids = ctx.dev_alloc(ids.nbytes), ctx.dev_alloc(hids.nbytes)
     ctx.h2d(d_ids, ids); ctx.h2d(d_hids, hids)
     dg = synth_desc(4, G, 60, 0, 0, row_ids=d_ids)
