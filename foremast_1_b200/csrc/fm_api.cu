@@ -67,6 +67,7 @@ struct RowCache {
   std::vector<uint8_t> miss;                // per row of the current call: has to be uploaded
   bool prev_clean = false;                  // every row of the previous call was resident when it ended
   bool any_miss = false;
+  uint32_t stamp_due = 0;                   // epoch of the last re-poll whose slots have not been stamped yet
   uint32_t* pin_slot = nullptr;             // prev_slot in pinned memory: its per-chunk uploads must not
   size_t pin_cap = 0;                       // stall the host behind the copy stream (pageable copies do)
   bool pin_fresh = false;                   // pin_slot == prev_slot
@@ -80,7 +81,7 @@ struct RowCache {
     pin_slot = nullptr; pin_cap = 0; pin_fresh = false;
     cap = 0; n_live = 0; hand = 0;
     slot_id.clear(); slot_epoch.clear(); slot_blen.clear(); slot_hlen.clear(); slot_live.clear();
-    index.clear(); prev_ids.clear(); prev_slot.clear(); miss.clear(); prev_clean = false;
+    index.clear(); prev_ids.clear(); prev_slot.clear(); miss.clear(); prev_clean = false; stamp_due = 0;
   }
 };
 
@@ -710,16 +711,22 @@ void cache_assign(RowCache& k, const fm_batch* b, const uint64_t* ids, uint64_t 
   if (++k.epoch == 0) {                                   // epoch wrapped: nobody is "in use"
     std::fill(k.slot_epoch.begin(), k.slot_epoch.end(), 0u);
     k.epoch = 1;
+    if (k.stamp_due) k.stamp_due = 1;
   }
   const uint64_t prev_n = k.prev_ids.size();
   if (k.prev_clean && prev_n == S && memcmp(ids, k.prev_ids.data(), S * sizeof(uint64_t)) == 0) {
-    for (uint64_t s = 0; s < S; ++s) k.slot_epoch[slot[s]] = k.epoch;
+    k.stamp_due = k.epoch;                                // "used in this call", written when somebody needs it
     k.hits += S;
     if (k.any_miss || miss.size() != S) miss.assign(S, 0);
     k.any_miss = false;
     return;
   }
   k.pin_fresh = false;
+  if (k.stamp_due) {                                      // the re-polls since the last full pass used these slots
+    for (uint64_t s = 0; s < prev_n && s < slot.size(); ++s)
+      if (slot[s] != RowCache::kNone) k.slot_epoch[slot[s]] = k.stamp_due;
+    k.stamp_due = 0;
+  }
   if (slot.size() < S) slot.resize(S);
   miss.assign(S, 0);
   k.any_miss = false;
