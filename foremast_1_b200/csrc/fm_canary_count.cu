@@ -634,7 +634,7 @@ __global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
     }
     // few distinct current values, most of them repeated: probably an error-count series, whose rank
     // integers come from its classes (ranks_by_classes): sweep 1 then elects instead of counting
-    const bool tie_cand = ranks && cur_runs <= a.tie_runs && 2u * cur_runs <= nc;
+    const bool tie_cand = ranks && (a.tie_runs >= 65u || (cur_runs <= a.tie_runs && 2u * cur_runs <= nc));   // 65: every series (tests)
 
     // ---- sweep 1 over the staged baseline: moments, election pass A -------------------------------
     // (the keys are NOT kept: sweep 2 reads the stage again, so that a lane holds a few keys at a

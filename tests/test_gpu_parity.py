@@ -16,11 +16,13 @@ from parity import assert_records_match, bound_masks
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module", params=["auto", "auto-tiny", "auto-1stage", "sort", "generic", "elect", "elect-1stage"])
+@pytest.fixture(scope="module", params=["auto", "auto-tiny", "auto-notie", "auto-alltie", "auto-1stage", "sort", "generic", "elect", "elect-1stage"])
 def ctx(request):
     """auto: the counting canary kernel (fm_canary_count.cu) wherever it applies; auto-tiny: the same
     with an election table of 64 slots, so that every series goes through all the overflow rounds and
-    the direct count behind them; auto-1stage: its free-running launch shape (no barrier per series); sort: the register-sort canary kernel (fm_canary_sort.cu); elect:
+    the direct count behind them; auto-notie: without the class path for heavily tied series (they then
+    pass the singleton filter with every key a suspect); auto-alltie: every series tries the class path
+    first (continuous ones fail it and fall back to the search path); auto-1stage: its free-running launch shape (no barrier per series); sort: the register-sort canary kernel (fm_canary_sort.cu); elect:
     the CTA-per-series election kernel (fm_canary_elect.cu); generic: the shared-memory sort kernel
     for everything (the FOREMAST_CUDA_* switches are read when the ctx is created)."""
     import os
@@ -30,8 +32,12 @@ def ctx(request):
     if request.param.endswith("tiny"):
         os.environ["FOREMAST_CUDA_SLOTS"] = "64"
         os.environ["FOREMAST_CUDA_STAGES"] = "0"
+    if request.param.endswith("notie"):
+        os.environ["FOREMAST_CUDA_TIE_RUNS"] = "0"
+    if request.param.endswith("alltie"):
+        os.environ["FOREMAST_CUDA_TIE_RUNS"] = "65"
     c = Context(0)
-    for k in ("FOREMAST_CUDA_PATH", "FOREMAST_CUDA_STAGES", "FOREMAST_CUDA_SLOTS"):
+    for k in ("FOREMAST_CUDA_PATH", "FOREMAST_CUDA_STAGES", "FOREMAST_CUDA_SLOTS", "FOREMAST_CUDA_TIE_RUNS"):
         os.environ.pop(k, None)
     yield c
     c.close()
