@@ -259,7 +259,7 @@ int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
     // a 16th resident warp is worth more than the last slots (measured, profiles/var_slots.sh: 1440-point
     // baselines 9.85 ms per 1M series with 896-944 slots and 16 warps, 10.1 ms with 1032 and 15): take
     // what 16 warps leave if that is still 9/16 of a slot per key
-    const size_t per_warp = (limit / 16) & ~size_t(127);
+    const size_t per_warp = (limit / (size_t)fm_canary_count_max_warps()) & ~size_t(127);
     const size_t fixed = fm_canary_count_fixed_bytes() + (size_t)(64 + cap) * 4;
     if (per_warp > fixed) {
       const uint32_t s16 = (uint32_t)((per_warp - fixed) / 8) & ~3u;
@@ -284,14 +284,15 @@ int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
     return FM_OK;
   }
   a.warp_bytes = (uint32_t)((fm_canary_count_fixed_bytes() + (size_t)(64 + cap) * 4 + (size_t)slots * 8 + 127) & ~size_t(127));
-  const int max_warps = c->count_warps ? c->count_warps : 16;     // 128 registers per thread
+  const int built_w = fm_canary_count_max_warps();                 // 16: 128 registers per thread
+  const int max_warps = c->count_warps ? std::min(c->count_warps, built_w) : built_w;
   int best_w = 1, best_total = 0;
   // ONE CTA per SM whose warps meet at a barrier per series, so that they share the instruction
   // fetches of the long loop body (+4 %); FOREMAST_CUDA_STAGES=1 (experiment): several free-running CTAs
   a.n_stages = c->force_stages == 1 ? 1u : 2u;
   a.sync_mask = (uint32_t)c->count_sync - 1u;
   a.tie_runs = (uint32_t)c->tie_runs;
-  const int w_hi = a.n_stages == 2u ? 16 : 8, w_lo = a.n_stages == 2u ? 2 : 1;
+  const int w_hi = a.n_stages == 2u ? built_w : 8, w_lo = a.n_stages == 2u ? 2 : 1;
   for (int w = w_lo; w <= w_hi; ++w) {
     const size_t cta = (size_t)w * a.warp_bytes;
     if (cta > limit) break;

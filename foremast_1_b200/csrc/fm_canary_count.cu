@@ -525,7 +525,10 @@ __device__ __noinline__ ModelOut model_call(const fm_global_params* g, const flo
   return o;
 }
 
-__global__ void __launch_bounds__(512, 1) k_canary_count(const FmKArgs a) {
+#ifndef FM_COUNT_MAXW
+#define FM_COUNT_MAXW 16
+#endif
+__global__ void __launch_bounds__(32 * FM_COUNT_MAXW, 1) k_canary_count(const FmKArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   // tier: NV vector rows (4 keys per lane each) + NS scalar rows of the staged baseline
   const uint32_t NV = a.cnt_nv, NS = a.cnt_ns;
@@ -1246,6 +1249,8 @@ uint32_t fm_canary_count_tier(uint32_t n_base, int* nv, int* ns) {
 }
 
 size_t fm_canary_count_fixed_bytes() { return 16 + kSearchBytes + kFinalBytes; }
+int fm_canary_count_max_warps() { return FM_COUNT_MAXW; }
+
 int fm_launch_canary_count(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st) {
   const size_t smem = (size_t)warps_per_cta * a.warp_bytes;
   k_canary_count<<<grid, warps_per_cta * 32, smem, st>>>(a);

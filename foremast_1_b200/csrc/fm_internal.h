@@ -76,6 +76,7 @@ cudaError_t fm_canary_sort_smem_attr(int bytes);
 int fm_launch_canary_elect(const FmKArgs& a, int nv, int grid, cudaStream_t st);
 // fm_canary_count.cu: tier = (vector rows, scalar rows) per lane; a.log_m carries the slot count
 int fm_launch_canary_count(const FmKArgs& a, int warps_per_cta, int grid, cudaStream_t st);
+int fm_canary_count_max_warps();   // warps per CTA the kernel is built for (its register budget)
 uint32_t fm_canary_count_tier(uint32_t n_base, int* nv, int* ns);
 size_t fm_canary_count_fixed_bytes();
 size_t fm_canary_team_fixed_bytes();
