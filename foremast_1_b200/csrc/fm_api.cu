@@ -111,6 +111,7 @@ struct fm_ctx {
   int ma_group = 0;                // FOREMAST_CUDA_MA_GROUP=4|8|16|32: lanes per series of k_ma_only
   int small_table = 0;             // FOREMAST_CUDA_SMALL_TABLE: elect path, load factor <= 0.8
   int count_sync = 4;              // FOREMAST_CUDA_COUNT_SYNC: trips between two CTA barriers of k_canary_count (power of two)
+  int count_wpc = 0;               // FOREMAST_CUDA_COUNT_WPC: warps per CTA of k_canary_count (several CTAs per SM share the warp budget)
   int tie_runs = 24;               // FOREMAST_CUDA_TIE_RUNS: see FmKArgs::tie_runs (0 switches the class path off)
   int force_gather = 0;            // FOREMAST_CUDA_GATHER: cached rows are copied into the chunk even for kernels that read the cache in place
   int chunk_mb = 0;                // FOREMAST_CUDA_CHUNK_MB: rows per pipelined chunk of fm_score_groups (default 64 MB)
@@ -294,6 +295,7 @@ int32_t plan_canary_count(fm_ctx* c, const fm_batch* b, Plan* pl) {
   a.tie_runs = (uint32_t)c->tie_runs;
   const int w_hi = a.n_stages == 2u ? built_w : 8, w_lo = a.n_stages == 2u ? 2 : 1;
   for (int w = w_lo; w <= w_hi; ++w) {
+    if (c->count_wpc && w != c->count_wpc) continue;       // experiment: CTA size forced
     const size_t cta = (size_t)w * a.warp_bytes;
     if (cta > limit) break;
     int ctas = (int)(sm_total / (cta + 1024));
@@ -511,6 +513,7 @@ int32_t fm_ctx_create(int32_t device, fm_ctx** out) {
   if (const char* e = getenv("FOREMAST_CUDA_MA_GROUP")) { const int v = atoi(e); c->ma_group = (v == 2 || v == 4 || v == 8 || v == 16 || v == 32) ? v : 0; }
   c->small_table = getenv("FOREMAST_CUDA_SMALL_TABLE") != nullptr;
   c->force_gather = getenv("FOREMAST_CUDA_GATHER") != nullptr;
+  if (const char* e = getenv("FOREMAST_CUDA_COUNT_WPC")) { const int v = atoi(e); if (v >= 2 && v <= 32) c->count_wpc = v; }
   if (const char* e = getenv("FOREMAST_CUDA_TIE_RUNS")) { const int v = atoi(e); if (v >= 0 && v <= 65) c->tie_runs = v; }
   if (const char* e = getenv("FOREMAST_CUDA_COUNT_SYNC")) { const int v = atoi(e); if (v >= 1 && v <= 1024 && (v & (v - 1)) == 0) c->count_sync = v; }
   if (const char* e = getenv("FOREMAST_CUDA_CHUNK_MB")) { const int v = atoi(e); c->chunk_mb = (v >= 1 && v <= 4096) ? v : 0; }
